@@ -1,0 +1,170 @@
+/* cudapt.h -- C ABI of the B200-native path-tracing backend (libcudapt.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of imisumi/software-path-tracer: the progressive
+ * per-pixel path-tracing loop behind render::PathTracer.  Every entry point cites the reference interface
+ * it replaces; paths are relative to the reference tree and "CPT.cpp" abbreviates
+ * libs/render/src/engines/pathtracer/backends/cpu/CPUPathTracer.cpp.
+ *
+ * Plain pointers and sizes only.  All functions return 0 on success and a non-zero cudapt_status
+ * otherwise; cudapt_last_error() then describes the failure.  There is no CPU fallback: every entry point
+ * that computes fails with CUDAPT_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Threading: one host thread per context (the reference is synchronous and non-reentrant, App.cpp:231).
+ * cudapt_render() only enqueues work on the context's stream; every read-back call synchronises.
+ */
+#ifndef CUDAPT_H_
+#define CUDAPT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUDAPT_ABI_VERSION 1
+
+typedef struct cudapt_ctx cudapt_ctx;
+
+typedef enum cudapt_status {
+  CUDAPT_OK = 0,
+  CUDAPT_ERR_INVALID = 1,   /* bad argument / call order (reference: verify() abort, render_assert.h:15-25) */
+  CUDAPT_ERR_CUDA = 2,      /* CUDA runtime error; never swallowed */
+  CUDAPT_ERR_NO_SCENE = 3,  /* render before any scene upload (reference: verify(m_scene) CPT.cpp:46) */
+  CUDAPT_ERR_NO_FRAMES = 4  /* resolve before any frame (reference: assert(m_frameCount>0) CPT.cpp:89) */
+} cudapt_status;
+
+/* RNG streams.  REFERENCE_PCG reproduces CPT.cpp:192-195 + :294-301 bit-for-bit (seed x + y*W +
+ * frame*982451653u, PCG hash step, float(w)/4294967295.0f).  PHILOX is Philox4x32-10 keyed by
+ * (0xB200CAFE, seed) with counter (pixel, sample, bounce, block): any GPU and the CPU oracle replay the
+ * same stream for a given (pixel, sample, bounce) irrespective of how work is partitioned. */
+typedef enum cudapt_rng_mode { CUDAPT_RNG_REFERENCE_PCG = 0, CUDAPT_RNG_PHILOX = 1 } cudapt_rng_mode;
+
+/* Material models of the mesh integrator (the reference has none: constant 0.7 albedo, CPT.cpp:260). */
+typedef enum cudapt_material_type {
+  CUDAPT_MAT_LAMBERT = 0,
+  CUDAPT_MAT_MIRROR = 1,
+  CUDAPT_MAT_DIELECTRIC = 2,
+  CUDAPT_MAT_GGX_COATED = 3
+} cudapt_material_type;
+
+/* 32-byte material record (two 128-bit loads on the device). */
+typedef struct cudapt_material {
+  float albedo[3];
+  uint32_t type;      /* cudapt_material_type */
+  float emission[3];  /* radiance emitted by the front face (geometric-normal side) */
+  float param;        /* GGX alpha for GGX_COATED, index of refraction for DIELECTRIC */
+} cudapt_material;
+
+/* Pinhole camera.  Defaults reproduce the camera hard-coded in CPT.cpp:62-73 bit-for-bit: origin 0,
+ * right +X, up +Y, forward +Z, tan(vfov/2) = 1, pixel-corner sampling, no jitter. */
+typedef struct cudapt_camera {
+  float origin[3];
+  float right[3];
+  float up[3];
+  float forward[3];
+  float tan_half_fov;
+} cudapt_camera;
+
+typedef struct cudapt_config {
+  int32_t device;            /* CUDA device ordinal */
+  int32_t rng_mode;          /* cudapt_rng_mode; default REFERENCE_PCG */
+  int32_t max_bounces;       /* default 4  (literal at CPT.cpp:199) */
+  int32_t rr_start;          /* default 2: Russian roulette once bounce_count > rr_start (CPT.cpp:264) */
+  float tnear;               /* default 1e-3f (CPT.cpp:221) */
+  float eps;                 /* default 1e-4f normal offset (CPT.cpp:277) */
+  float albedo;              /* default 0.7f, sphere integrator only (CPT.cpp:260) */
+  float sky_scale;           /* default 1: multiplies the procedural sky (CPT.cpp:286-292) */
+  uint32_t seed;             /* Philox key word 1 */
+  int32_t jitter;            /* default 0: sub-pixel jitter (Philox mode only); 0 = reference corner sampling */
+  int32_t nee;               /* default 0: next-event estimation on emissive triangles (mesh integrator) */
+  int32_t samples_per_pass;  /* default 1: samples of every pixel traced together by the wavefront */
+} cudapt_config;
+
+typedef struct cudapt_stats {
+  uint64_t paths;            /* camera samples traced to termination since the last reset */
+  uint64_t rays;             /* closest-hit + shadow queries since the last reset (counted on device) */
+  uint64_t nodes_visited;    /* BVH nodes fetched   (only while cudapt_set_counting(ctx,1)) */
+  uint64_t tris_tested;      /* triangles tested    (only while cudapt_set_counting(ctx,1)) */
+  uint64_t shade_invocations;/* surface interactions shaded */
+  uint64_t kernel_launches;  /* kernels launched by this library since the last reset */
+  double render_ms;          /* CUDA-event time of all cudapt_render() calls since the last reset */
+  double last_render_ms;     /* CUDA-event time of the most recent cudapt_render() call */
+  double accel_build_ms;     /* host wall time of the last cudapt_build_accel() */
+  uint64_t accel_bytes;      /* device bytes of BVH nodes + packed triangles */
+  uint32_t frame_count;      /* samples accumulated per pixel (reference m_frameCount, CPT.h:68) */
+  uint32_t n_triangles;
+  uint32_t n_nodes;
+  uint32_t n_spheres;
+} cudapt_stats;
+
+/* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */
+void cudapt_default_config(cudapt_config* cfg);
+void cudapt_default_camera(cudapt_camera* cam);
+int cudapt_create(const cudapt_config* cfg, cudapt_ctx** out);
+void cudapt_destroy(cudapt_ctx* ctx);
+/* Error text of the last failing call on ctx (ctx may be NULL for a failed cudapt_create). */
+const char* cudapt_last_error(const cudapt_ctx* ctx);
+int cudapt_abi_version(void);
+
+/* ---- settings: invalidate() size rule, CPT.cpp:140-149 --------------------------------------------- */
+/* (Re)allocates accumulation float4[W*H] and result u32[W*H], zeroes them, frame count = 0. */
+int cudapt_set_resolution(cudapt_ctx* ctx, uint32_t width, uint32_t height);
+/* Replaces the integrator parameters (everything in cfg except .device) and restarts accumulation,
+ * like a dirty RenderSettings does (CPT.cpp:132-138). */
+int cudapt_set_config(cudapt_ctx* ctx, const cudapt_config* cfg);
+int cudapt_set_camera(cudapt_ctx* ctx, const cudapt_camera* cam);
+
+/* ---- scene upload: rebuild_scene(), CPT.cpp:362-403 ------------------------------------------------ */
+/* n spheres as {cx,cy,cz,r} (the float4 the reference hands to Embree, CPT.cpp:377-385) plus the
+ * caller's stable id per sphere (render::NodeID) reported by cudapt_read_primary_hits.  Replaces any
+ * previous scene ("rebuild = replace") and restarts accumulation.  Selects the sphere integrator. */
+int cudapt_upload_spheres(cudapt_ctx* ctx, const float* center_radius, const uint32_t* node_id, uint32_t n);
+/* Triangle scene (no reference analogue; configs 2-5).  vertices: nv x float3; indices: nt x uint3;
+ * material_id: nt (may be NULL = all 0).  Selects the mesh (wavefront) integrator once built. */
+int cudapt_upload_mesh(cudapt_ctx* ctx, const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt,
+                       const uint32_t* material_id);
+int cudapt_upload_materials(cudapt_ctx* ctx, const cudapt_material* materials, uint32_t n);
+/* Builds the 8-wide quantised BVH on the host (SAH) and uploads it; replaces rtcCommitScene (CPT.cpp:403). */
+int cudapt_build_accel(cudapt_ctx* ctx);
+
+/* ---- progressive rendering: render(), CPT.cpp:43-85 ------------------------------------------------ */
+/* Zero the accumulation buffer, frame count = 0 (CPT.cpp:151-154). */
+int cudapt_reset(cudapt_ctx* ctx);
+/* Enqueue n_frames frames of 1 sample per pixel each.  Frame f (1-based, = frame_count+1 as at
+ * CPT.cpp:61) seeds the RNG; frame_count advances by n_frames. */
+int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames);
+int cudapt_synchronize(cudapt_ctx* ctx);
+
+/* ---- read-back: get_render_result(), CPT.cpp:87-117 + Color.h:7-10 --------------------------------- */
+/* accum/frame_count -> clamp[0,1] -> (uint8)(c*255) -> R<<24|G<<16|B<<8|A, W*H words, row 0 on top. */
+int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out);
+/* Float accumulation (private m_accumulation_buffer, CPT.h:72): 4*W*H floats RGBA, and the frame count. */
+int cudapt_read_accum(cudapt_ctx* ctx, float* host_out, uint32_t* frame_count);
+/* Restore a previously read state (checkpoint/resume, merging partial renders). */
+int cudapt_write_accum(cudapt_ctx* ctx, const float* host_in, uint32_t frame_count);
+/* Primary-hit AOV of the first sample: caller id of the primitive hit (sphere node_id, or triangle
+ * index; 0xFFFFFFFF = miss) and ray parameter t (+inf on miss).  Either pointer may be NULL. */
+int cudapt_read_primary_hits(cudapt_ctx* ctx, uint32_t* prim_id, float* t);
+int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out);
+/* Enable device-side node/triangle counters (slower instrumented traversal; off by default). */
+int cudapt_set_counting(cudapt_ctx* ctx, int enabled);
+
+/* ---- multi-GPU partitioning (no reference analogue) ----------------------------------- */
+/* Interleaved image tiles: this context renders only tiles t with (t + tile_row) % world == rank, where
+ * tiles are tile_w x tile_h pixels in raster order.  Pixels it does not own stay exactly 0 in the
+ * accumulation buffer, so a sum over ranks is bit-identical to a single-GPU render.  world = 1 disables. */
+int cudapt_set_tile_partition(cudapt_ctx* ctx, uint32_t rank, uint32_t world, uint32_t tile_w, uint32_t tile_h);
+/* Sample ranges: frame k of this context (k = 0,1,..) uses the global 1-based frame index
+ * first + k*stride for RNG seeding.  Default first = 1, stride = 1. */
+int cudapt_set_frame_range(cudapt_ctx* ctx, uint32_t first, uint32_t stride);
+/* Device pointers for the caller's collective (NCCL reduce at read-back boundaries) and timing. */
+void* cudapt_accum_device_ptr(cudapt_ctx* ctx);  /* float4[W*H] */
+void* cudapt_stream(cudapt_ctx* ctx);            /* cudaStream_t all work is enqueued on */
+/* Declare that the accumulation buffer now holds frame_count samples per pixel (after an external reduce). */
+int cudapt_set_frame_count(cudapt_ctx* ctx, uint32_t frame_count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUDAPT_H_ */
