@@ -1,0 +1,385 @@
+#!/usr/bin/env python
+"""bench.py -- Msamples/s (paths/s) of the path-tracing hot path on N B200s, next to the CPU path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4] [--impl b200|reference]
+
+A "step" = one full progressive render of the workload (reset, spp frames of 1 sample/pixel each) on every
+rank; at N > 1 each rank renders its own sample range (rank g: global frames g+1, g+1+N, ...; weak scaling:
+per-GPU work fixed) and the float accumulation buffers are summed to rank 0 with one NCCL reduce at the
+read-back boundary, inside the step.  One JSON line is printed by rank 0 (contract in the task statement).
+
+Timing: per-step CUDA-event pairs recorded on the stream libcudapt launches on; L2 is flushed (256 MiB memset)
+between steps, outside the event pairs; the reported time is the max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (description, width, height, spp, config overrides, camera tan_half_fov)
+    "c1": dict(desc="configs[0]: App.cpp 38-sphere scene, 640x360, 16 spp, reference constants (PCG, 4 bounces)",
+               w=640, h=360, spp=16, cfg=dict(), fov=1.0, kind="spheres"),
+    "c2": dict(desc="configs[1]: Cornell box mesh (diffuse+mirror+dielectric), 1280x720, 256 spp, area-light NEE, depth 8",
+               w=1280, h=720, spp=256, cfg=dict(rng_mode=1, max_bounces=8, sky_scale=0.0, jitter=1, nee=1, seed=2,
+                                                samples_per_pass=4), fov=0.36, kind="mesh"),
+    "c3": dict(desc="configs[2]: 1,002,528-triangle fBm height field, GGX-coated, 1920x1080, 64 spp, depth 8",
+               w=1920, h=1080, spp=64, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=4),
+               fov=1.0, kind="mesh"),
+    "c4": dict(desc="configs[3]: 20,000,002-triangle flattened rock field (BVH > L2), 1920x1080, 128 spp, depth 16",
+               w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=4),
+               fov=1.0, kind="mesh"),
+}
+DEFAULT_WORKLOAD = "c1"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def build_scene(scenes, wl):
+    if wl["kind"] == "spheres":
+        return dict(spheres=scenes.app_spheres())
+    name = wl["name"]
+    if name == "c2":
+        v, t, m, mats = scenes.cornell_box()
+    elif name == "c3":
+        v, t, m, mats = scenes.heightfield()
+    else:
+        v, t, m, mats = scenes.rock_field()
+    return dict(v=v, t=t, m=m, mats=mats)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                mx.append(float(f[1]))
+                if t0 - 0.05 <= ts <= t1 + 0.15:
+                    sm.append(float(f[0]))
+                    for n, val in zip(names, f[3:7]):
+                        if val.lower().startswith("active"):
+                            reasons.add(n)
+            except ValueError:
+                continue
+        if not sm and self.rows:  # region shorter than the sampling period: take the nearest sample
+            try:
+                sm = [float(self.rows[-1][1].split(",")[0])]
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own CPU implementation of the path (oracle/_ref) or, for the mesh workloads the
+# reference cannot render (CPUPathTracer.cpp:367-398: spheres only), the CPU twin on all host threads.
+# ------------------------------------------------------------------------------------------------------
+def cpu_sample(wl, scene, budget_s=12.0):
+    """One bounded CPU sample of the workload.  Returns (samples, seconds, rays, kind, cores, description)."""
+    oracle = importlib.import_module("oracle")
+    W, H = wl["w"], wl["h"]
+    if wl["kind"] == "spheres":
+        if oracle.ref_available():
+            s = oracle.RefSession(scene["spheres"], W, H)
+            s.render(1)  # first call builds the scene (rebuild_scene); not timed, as on the GPU side
+            r0 = s.rays
+            frames = wl["spp"]
+            sec = s.render(frames, True)  # render() + get_render_result() per frame, as App::run does
+            n, rays = W * H * frames, s.rays - r0
+            s.close()
+            return n, sec, rays, "reference", 1, (f"unmodified reference CPUPathTracer + Embree stand-in, {W}x{H}, "
+                                                  f"{frames} frames incl. get_render_result() each, 1 thread "
+                                                  "(the reference render loop is single-threaded)")
+        p = oracle.twin_params(W, H, threads=1)
+        t0 = time.time()
+        _, _, _, c = oracle.twin_render_spheres(p, scene["spheres"], wl["spp"])
+        return W * H * wl["spp"], time.time() - t0, c.rays, "port", 1, f"CPU twin, {W}x{H}, {wl['spp']} frames, 1 thread"
+    # mesh: twin on all host threads, at reduced resolution / spp sized for ~budget_s
+    cores = os.cpu_count() or 1
+    mesh = scene.get("_twin_mesh")
+    if mesh is None:
+        mesh = oracle.TwinMesh(scene["v"], scene["t"], scene["m"], scene["mats"])
+        scene["_twin_mesh"] = mesh
+    sw, sh = max(W // 4, 16), max(H // 4, 9)
+    cfg = dict(wl["cfg"])
+    cfg.pop("samples_per_pass", None)
+    p = oracle.twin_params(sw, sh, cam_tan_half_fov=wl["fov"], **cfg)
+    t0 = time.time()
+    _, _, _, c = mesh.render(p, 1)
+    probe = time.time() - t0
+    frames = int(max(1, min(64, budget_s / max(probe, 1e-3))))
+    t0 = time.time()
+    _, _, _, c = mesh.render(p, frames, first_frame=2)
+    sec = time.time() - t0
+    return sw * sh * frames, sec, c.rays, "port", cores, (f"CPU twin (own BVH2), same scene and integrator, {sw}x{sh} "
+                                                          f"(1/16 of the pixels), {frames} spp, {cores} threads")
+
+
+def run_reference_arm(args, wl, scene, rank, world):
+    if rank != 0:
+        return
+    vals, secs, last = [], [], None
+    for i in range(args.warmup + args.steps):
+        last = cpu_sample(wl, scene, budget_s=max(2.0, 40.0 / (args.warmup + args.steps)))
+        if i >= args.warmup:
+            vals.append(last[0])
+            secs.append(last[1])
+    n, sec, rays, kind, cores, desc = last
+    value = sum(vals) / sum(secs) / 1e6
+    line = {
+        "impl": "reference", "metric": "Msamples/s (paths/s)", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "name": wl["name"]},
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc,
+                         "mrays_per_s": rays / sec / 1e6},
+        "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = dict(WORKLOADS[args.workload], name=args.workload)
+    if args.spp:
+        wl["spp"] = args.spp
+    scenes = importlib.import_module("software-path-tracer_b200.scenes")
+
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference_arm(args, wl, build_scene(scenes, wl), rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    pt = importlib.import_module("software-path-tracer_b200")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    scene = build_scene(scenes, wl)
+    W, H, spp = wl["w"], wl["h"], wl["spp"]
+    cfg = pt.default_config(device=local_rank, **wl["cfg"])
+    tr = pt.PathTracer(cfg)
+    tr.set_camera(pt.default_camera(tan_half_fov=wl["fov"]))
+    tr.set_resolution(W, H)
+    if wl["kind"] == "spheres":
+        tr.upload_spheres(scene["spheres"])
+        scene_bytes = scene["spheres"].nbytes + 4 * len(scene["spheres"])
+    else:
+        tr.upload_mesh(scene["v"], scene["t"], scene["m"], scene["mats"])
+        scene_bytes = int(tr.stats().accel_bytes)
+    if world > 1:
+        tr.set_frame_range(rank + 1, world)  # sample-range sharding
+
+    stream = torch.cuda.ExternalStream(tr.stream_handle, device=local_rank)
+    n_px = W * H
+    accum_t = None
+    if world > 1:
+        # zero-copy view of libcudapt's accumulation buffer for the NCCL reduce
+        class _Cai:
+            __cuda_array_interface__ = {"shape": (n_px * 4,), "typestr": "<f4", "data": (tr.accum_device_ptr, False),
+                                        "version": 2}
+        accum_t = torch.as_tensor(_Cai(), device=f"cuda:{local_rank}")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
+
+    def step():
+        tr.reset()
+        tr.render(spp)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+
+    def sync_all():
+        tr.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    launches0 = tr.stats().kernel_launches
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    time.sleep(0.25) if sampler else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_wall0 = time.time()
+    for k in range(args.steps):
+        flush.zero_()                      # L2 flush, on torch's stream, outside the event pair
+        torch.cuda.synchronize()
+        ev[k][0].record(stream)
+        step()
+        ev[k][1].record(stream)
+    sync_all()
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    st = tr.stats()
+    launches = st.kernel_launches - launches0
+    # dominant-kernel time from the library's own event pair around cudapt_render (same stream)
+    render_ms = st.last_render_ms
+    paths_per_step = n_px * spp
+    value = world * paths_per_step * args.steps / (total_ms * 1e-3) / 1e6
+    rays_per_path = st.rays / max(st.paths, 1)
+
+    # ---- e2e through the C ABI with host buffers: scene H2D + render + resolve + RGBA8 D2H every step ----
+    host_rgba = np.empty((H, W), np.uint32)
+
+    def e2e_step():
+        if wl["kind"] == "spheres":
+            tr.upload_spheres(scene["spheres"])     # H2D of the step's scene; also restarts accumulation
+        else:
+            tr.reupload_scene()
+        tr.render(spp)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+            tr.set_frame_count(spp * world if rank == 0 else spp)
+        tr.resolve_rgba8(host_rgba)                  # resolve kernel + D2H + sync
+
+    e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = world * paths_per_step * args.steps / float(e2e_s.item()) / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_peak, peak_src = load_peaks()
+    roof = roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src)
+    line = {
+        "metric": "Msamples/s (paths/s)", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "name": wl["name"], "width": W, "height": H, "spp_per_gpu": spp,
+                   "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
+                   "partition": "one process per GPU; sample ranges per rank; NCCL reduce(sum) of the float "
+                                "accumulation buffer to rank 0 at the end of every step" if world > 1 else "single GPU"},
+        "mrays_per_s": value * rays_per_path, "rays_per_path": rays_per_path,
+        "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(scene_bytes),
+                "d2h_bytes_per_step": int(n_px * 4)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roof,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        n, sec, rays, kind, cores, desc = cpu_sample(wl, scene)
+        line["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Msamples/s", "cores": cores, "kind": kind,
+                                "sample": desc, "mrays_per_s": rays / sec / 1e6}
+    print(json.dumps(line), flush=True)
+    tr.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
+    """Algorithmic bytes per launch / CUDA-event duration of the render launch (DESIGN.md 'Roofline')."""
+    W, H, spp = wl["w"], wl["h"], wl["spp"]
+    n_px = W * H
+    if wl["kind"] == "spheres":
+        # one launch renders all spp frames: accumulation read + write once per pixel (32 B) + the scene once per CTA
+        alg_bytes = 32.0 * n_px
+        note = ("sphere megakernel: scene is in shared memory, the only compulsory HBM traffic is the 32 B/pixel "
+                "accumulation RMW per launch; the kernel is FP32/FP64-issue bound, not HBM bound -- see 'compute'")
+        rays = st.rays / max(st.frame_count, 1) * spp if st.frame_count else 0
+        n_sph = len(scene["spheres"])
+        flops = (st.rays / max(st.paths, 1)) * (25.0 * n_sph + 12.0) + (st.shade_invocations / max(st.paths, 1)) * 90.0
+        achieved = alg_bytes / (render_ms * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": None, "peak_source": peak_src, "note": note,
+                "compute": {"flops_per_path": flops, "achieved_tflops": flops * n_px * spp / (render_ms * 1e-3) / 1e12,
+                            "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12}}
+    paths = max(st.paths, 1)
+    R = st.rays / paths
+    B = st.shade_invocations / paths
+    counted = getattr(tr, "_counted", None)
+    Nn = counted["nodes_per_ray"] if counted else None
+    Nt = counted["tris_per_ray"] if counted else None
+    if Nn is None:
+        return {"bound": "hbm", "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None, "traffic": None,
+                "peak_source": peak_src, "note": "node/triangle counters unavailable"}
+    bytes_per_path = R * (Nn * 80.0 + Nt * 48.0) + B * 160.0 + 32.0
+    alg_bytes = bytes_per_path * n_px * spp
+    achieved = alg_bytes / (render_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+            "traffic": None, "peak_source": peak_src, "bytes_per_path": bytes_per_path, "R": R, "Nn": Nn, "Nt": Nt, "B": B}
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,520 @@
+// C ABI of libcudapt.so (include/cudapt.h): context, device buffers, launches.  Host C++ only; the
+// kernels live in spheres.cu / wavefront.cu / trace_bvh.cu.  "CPT.cpp" = the reference's
+// libs/render/src/engines/pathtracer/backends/cpu/CPUPathTracer.cpp.
+#include "../../include/cudapt.h"
+
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "mesh_host.h"
+
+using namespace cudapt;
+
+struct cudapt_ctx {
+  cudapt_config cfg{};
+  cudapt_camera cam{};
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  int sm_count = 0;
+
+  uint32_t width = 0, height = 0;
+  float4* d_accum = nullptr;
+  uint32_t* d_rgba = nullptr;
+  uint32_t* d_aov_prim = nullptr;
+  float* d_aov_t = nullptr;
+  unsigned long long* d_counters = nullptr;
+  uint32_t* h_pinned_rgba = nullptr;  // pinned staging for the 8-bit read-back
+  size_t pinned_pixels = 0;
+
+  // scene
+  enum SceneKind { kNone, kSpheres, kMesh } scene = kNone;
+  float4* d_spheres = nullptr;
+  uint32_t* d_node_id = nullptr;
+  uint32_t n_spheres = 0;
+  MeshScene mesh;  // host staging + device BVH / wavefront state (mesh_host.h)
+
+  // progressive state (CPT.h:68)
+  uint32_t frame_count = 0;
+  uint32_t frame_first = 1, frame_stride = 1;
+  uint32_t part_rank = 0, part_world = 1, tile_w = 32, tile_h = 32;
+  bool counting = false;
+
+  // stats
+  uint64_t launches = 0;
+  double render_ms = 0.0, last_render_ms = 0.0;
+  bool timing_pending = false;
+};
+
+namespace {
+
+thread_local std::string g_create_error;
+
+int fail(cudapt_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx)
+    ctx->err = buf;
+  else
+    g_create_error = buf;
+  return code;
+}
+
+#define CU_TRY(ctx, expr)                                                                              \
+  do {                                                                                                 \
+    cudaError_t e__ = (expr);                                                                          \
+    if (e__ != cudaSuccess)                                                                            \
+      return fail(ctx, CUDAPT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+bool valid_config(const cudapt_config& c) {
+  return c.max_bounces >= 1 && c.max_bounces <= 64 && c.rr_start >= 0 && c.samples_per_pass >= 1 &&
+         c.samples_per_pass <= 64 && (c.rng_mode == CUDAPT_RNG_REFERENCE_PCG || c.rng_mode == CUDAPT_RNG_PHILOX);
+}
+
+CameraParams camera_params(const cudapt_camera& c) {
+  CameraParams p;
+  p.origin = mk3(c.origin[0], c.origin[1], c.origin[2]);
+  p.right = mk3(c.right[0], c.right[1], c.right[2]);
+  p.up = mk3(c.up[0], c.up[1], c.up[2]);
+  p.forward = mk3(c.forward[0], c.forward[1], c.forward[2]);
+  p.tan_half_fov = c.tan_half_fov;
+  return p;
+}
+
+ImageParams image_params(const cudapt_ctx* ctx) {
+  ImageParams im;
+  im.width = ctx->width;
+  im.height = ctx->height;
+  im.inv_width = 1.0f / (float)ctx->width;    // CPT.cpp:54
+  im.inv_height = 1.0f / (float)ctx->height;  // CPT.cpp:53
+  im.aspect = (float)ctx->width / (float)ctx->height;  // CPT.cpp:65
+  im.part_rank = ctx->part_rank;
+  im.part_world = ctx->part_world;
+  im.tile_w = ctx->tile_w;
+  im.tile_h = ctx->tile_h;
+  im.tiles_x = (ctx->width + ctx->tile_w - 1) / ctx->tile_w;
+  return im;
+}
+
+IntegratorParams integrator_params(const cudapt_config& c) {
+  IntegratorParams ip;
+  ip.rng_mode = c.rng_mode;
+  ip.max_bounces = c.max_bounces;
+  ip.rr_start = c.rr_start;
+  ip.jitter = c.jitter;
+  ip.nee = c.nee;
+  ip.tnear = c.tnear;
+  ip.eps = c.eps;
+  ip.albedo = c.albedo;
+  ip.sky_scale = c.sky_scale;
+  ip.seed = c.seed;
+  return ip;
+}
+
+int restart_accumulation(cudapt_ctx* ctx) {  // CPT.cpp:151-154
+  if (ctx->d_accum) CU_TRY(ctx, cudaMemsetAsync(ctx->d_accum, 0, sizeof(float4) * (size_t)ctx->width * ctx->height, ctx->stream));
+  ctx->frame_count = 0;
+  return CUDAPT_OK;
+}
+
+int finish_timing(cudapt_ctx* ctx) {
+  if (!ctx->timing_pending) return CUDAPT_OK;
+  CU_TRY(ctx, cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  CU_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->last_render_ms = ms;
+  ctx->render_ms += ms;
+  ctx->timing_pending = false;
+  return CUDAPT_OK;
+}
+
+void free_spheres(cudapt_ctx* ctx) {
+  cudaFree(ctx->d_spheres);
+  cudaFree(ctx->d_node_id);
+  ctx->d_spheres = nullptr;
+  ctx->d_node_id = nullptr;
+  ctx->n_spheres = 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cudapt_abi_version(void) { return CUDAPT_ABI_VERSION; }
+
+void cudapt_default_config(cudapt_config* c) {
+  std::memset(c, 0, sizeof(*c));
+  c->device = 0;
+  c->rng_mode = CUDAPT_RNG_REFERENCE_PCG;
+  c->max_bounces = 4;   // CPT.cpp:199
+  c->rr_start = 2;      // CPT.cpp:264
+  c->tnear = 0.001f;    // CPT.cpp:221
+  c->eps = 1e-4f;       // CPT.cpp:277
+  c->albedo = 0.7f;     // CPT.cpp:260
+  c->sky_scale = 1.0f;
+  c->seed = 0;
+  c->jitter = 0;
+  c->nee = 0;
+  c->samples_per_pass = 1;
+}
+
+void cudapt_default_camera(cudapt_camera* cam) {  // CPT.cpp:62-73
+  std::memset(cam, 0, sizeof(*cam));
+  cam->right[0] = 1.0f;
+  cam->up[1] = 1.0f;
+  cam->forward[2] = 1.0f;
+  cam->tan_half_fov = 1.0f;
+}
+
+const char* cudapt_last_error(const cudapt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int cudapt_create(const cudapt_config* cfg, cudapt_ctx** out) {
+  if (!out) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_create: out is NULL");
+  *out = nullptr;
+  cudapt_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    cudapt_default_config(&c);
+  if (!valid_config(c)) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_create: invalid config");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return fail(nullptr, CUDAPT_ERR_CUDA, "cudapt_create: no CUDA device (%s); this backend has no CPU fallback",
+                cudaGetErrorString(e));
+  if (c.device < 0 || c.device >= n_dev) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_create: device %d of %d", c.device, n_dev);
+  cudaDeviceProp prop;
+  CU_TRY(nullptr, cudaGetDeviceProperties(&prop, c.device));
+  if (prop.major != 10)
+    return fail(nullptr, CUDAPT_ERR_CUDA, "cudapt_create: device %d is sm_%d%d; libcudapt is built for sm_100a only", c.device,
+                prop.major, prop.minor);
+  CU_TRY(nullptr, cudaSetDevice(c.device));
+  cudapt_ctx* ctx = new (std::nothrow) cudapt_ctx();
+  if (!ctx) return fail(nullptr, CUDAPT_ERR_INVALID, "out of host memory");
+  ctx->cfg = c;
+  ctx->sm_count = prop.multiProcessorCount;
+  cudapt_default_camera(&ctx->cam);
+  ctx->mesh.sm_count = ctx->sm_count;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+      cudaMalloc(&ctx->d_counters, sizeof(unsigned long long) * kCntSlots) != cudaSuccess ||
+      cudaMemset(ctx->d_counters, 0, sizeof(unsigned long long) * kCntSlots) != cudaSuccess) {
+    fail(nullptr, CUDAPT_ERR_CUDA, "cudapt_create: stream/event/counter setup failed: %s", cudaGetErrorString(cudaGetLastError()));
+    cudapt_destroy(ctx);
+    return CUDAPT_ERR_CUDA;
+  }
+  *out = ctx;
+  return CUDAPT_OK;
+}
+
+void cudapt_destroy(cudapt_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->cfg.device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  free_spheres(ctx);
+  ctx->mesh.release();
+  cudaFree(ctx->d_accum);
+  cudaFree(ctx->d_rgba);
+  cudaFree(ctx->d_aov_prim);
+  cudaFree(ctx->d_aov_t);
+  cudaFree(ctx->d_counters);
+  if (ctx->h_pinned_rgba) cudaFreeHost(ctx->h_pinned_rgba);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int cudapt_set_resolution(cudapt_ctx* ctx, uint32_t width, uint32_t height) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (width == 0 || height == 0 || (uint64_t)width * height > (1ull << 28))
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_set_resolution: bad size %ux%u", width, height);
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  if (width != ctx->width || height != ctx->height || !ctx->d_accum) {  // CPT.cpp:140-149
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_accum);
+    cudaFree(ctx->d_rgba);
+    cudaFree(ctx->d_aov_prim);
+    cudaFree(ctx->d_aov_t);
+    ctx->d_accum = nullptr, ctx->d_rgba = nullptr, ctx->d_aov_prim = nullptr, ctx->d_aov_t = nullptr;
+    const size_t n = (size_t)width * height;
+    CU_TRY(ctx, cudaMalloc(&ctx->d_accum, sizeof(float4) * n));
+    CU_TRY(ctx, cudaMalloc(&ctx->d_rgba, sizeof(uint32_t) * n));
+    CU_TRY(ctx, cudaMalloc(&ctx->d_aov_prim, sizeof(uint32_t) * n));
+    CU_TRY(ctx, cudaMalloc(&ctx->d_aov_t, sizeof(float) * n));
+    if (ctx->pinned_pixels < n) {
+      if (ctx->h_pinned_rgba) cudaFreeHost(ctx->h_pinned_rgba);
+      ctx->h_pinned_rgba = nullptr;
+      CU_TRY(ctx, cudaMallocHost(&ctx->h_pinned_rgba, sizeof(uint32_t) * n));
+      ctx->pinned_pixels = n;
+    }
+    ctx->width = width;
+    ctx->height = height;
+    ctx->mesh.invalidate_image_state();
+  }
+  CU_TRY(ctx, cudaMemsetAsync(ctx->d_aov_prim, 0xFF, sizeof(uint32_t) * (size_t)width * height, ctx->stream));
+  CU_TRY(ctx, cudaMemsetAsync(ctx->d_aov_t, 0, sizeof(float) * (size_t)width * height, ctx->stream));
+  return restart_accumulation(ctx);
+}
+
+int cudapt_set_config(cudapt_ctx* ctx, const cudapt_config* cfg) {
+  if (!ctx || !cfg) return CUDAPT_ERR_INVALID;
+  if (!valid_config(*cfg)) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_set_config: invalid config");
+  const int dev = ctx->cfg.device;
+  const bool spp_changed = cfg->samples_per_pass != ctx->cfg.samples_per_pass;
+  ctx->cfg = *cfg;
+  ctx->cfg.device = dev;
+  if (spp_changed) ctx->mesh.invalidate_image_state();
+  CU_TRY(ctx, cudaSetDevice(dev));
+  return restart_accumulation(ctx);  // CPT.cpp:132-138
+}
+
+int cudapt_set_camera(cudapt_ctx* ctx, const cudapt_camera* cam) {
+  if (!ctx || !cam) return CUDAPT_ERR_INVALID;
+  ctx->cam = *cam;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  return restart_accumulation(ctx);
+}
+
+int cudapt_upload_spheres(cudapt_ctx* ctx, const float* center_radius, const uint32_t* node_id, uint32_t n) {
+  if (!ctx || (n && !center_radius)) return CUDAPT_ERR_INVALID;
+  if ((size_t)n * sizeof(float4) > 200 * 1024)
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_upload_spheres: %u spheres exceed the shared-memory scene (12800)", n);
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  free_spheres(ctx);  // rebuild = replace (the reference re-attaches without detaching, CPT.cpp:362-403)
+  std::vector<uint32_t> ids(n);
+  for (uint32_t i = 0; i < n; ++i) ids[i] = node_id ? node_id[i] : i;
+  CU_TRY(ctx, cudaMalloc(&ctx->d_spheres, sizeof(float4) * (n ? n : 1)));
+  CU_TRY(ctx, cudaMalloc(&ctx->d_node_id, sizeof(uint32_t) * (n ? n : 1)));
+  if (n) {
+    CU_TRY(ctx, cudaMemcpy(ctx->d_spheres, center_radius, sizeof(float4) * n, cudaMemcpyHostToDevice));
+    CU_TRY(ctx, cudaMemcpy(ctx->d_node_id, ids.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice));
+  }
+  ctx->n_spheres = n;
+  ctx->scene = cudapt_ctx::kSpheres;
+  return restart_accumulation(ctx);
+}
+
+int cudapt_upload_mesh(cudapt_ctx* ctx, const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt,
+                       const uint32_t* material_id) {
+  if (!ctx || !vertices || !indices || nt == 0 || nv == 0) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_upload_mesh: empty mesh");
+  for (size_t i = 0; i < (size_t)nt * 3; ++i)
+    if (indices[i] >= nv) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_upload_mesh: index %u out of range", indices[i]);
+  ctx->mesh.set_mesh(vertices, nv, indices, nt, material_id);
+  return CUDAPT_OK;
+}
+
+int cudapt_upload_materials(cudapt_ctx* ctx, const cudapt_material* materials, uint32_t n) {
+  if (!ctx || (n && !materials)) return CUDAPT_ERR_INVALID;
+  ctx->mesh.set_materials(materials, n);
+  return CUDAPT_OK;
+}
+
+int cudapt_build_accel(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->mesh.has_host_mesh()) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_build_accel: no mesh uploaded");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::string err;
+  if (!ctx->mesh.build_and_upload(&err)) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_build_accel: %s", err.c_str());
+  ctx->scene = cudapt_ctx::kMesh;
+  return restart_accumulation(ctx);
+}
+
+int cudapt_reset(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  int rc = finish_timing(ctx);
+  if (rc) return rc;
+  CU_TRY(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long) * kCntSlots, ctx->stream));
+  ctx->launches = 0;
+  ctx->render_ms = 0.0;
+  ctx->last_render_ms = 0.0;
+  return restart_accumulation(ctx);
+}
+
+int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (ctx->scene == cudapt_ctx::kNone) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_render: scene not set before rendering");
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_render: resolution not set");
+  if (n_frames == 0) return CUDAPT_OK;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  int rc = finish_timing(ctx);
+  if (rc) return rc;
+  const uint32_t first = ctx->frame_first + ctx->frame_count * ctx->frame_stride;  // 1-based (CPT.cpp:61)
+  const bool want_aov = ctx->frame_count == 0;
+  CU_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  if (ctx->scene == cudapt_ctx::kSpheres) {
+    SphereLaunch a;
+    a.spheres = ctx->d_spheres;
+    a.node_id = ctx->d_node_id;
+    a.n_spheres = (int)ctx->n_spheres;
+    a.accum = ctx->d_accum;
+    a.aov_prim = want_aov ? ctx->d_aov_prim : nullptr;
+    a.aov_t = want_aov ? ctx->d_aov_t : nullptr;
+    a.counters = ctx->d_counters;
+    a.first_frame = first;
+    a.n_frames = n_frames;
+    a.frame_stride = ctx->frame_stride;
+    a.cam = camera_params(ctx->cam);
+    a.im = image_params(ctx);
+    a.ip = integrator_params(ctx->cfg);
+    CU_TRY(ctx, launch_render_spheres(a, ctx->cfg.rng_mode == CUDAPT_RNG_PHILOX, ctx->stream));
+    ctx->launches += 1;
+  } else {
+    if (ctx->cfg.rng_mode != CUDAPT_RNG_PHILOX)
+      return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_render: the mesh integrator requires CUDAPT_RNG_PHILOX");
+    MeshRenderArgs ra;
+    ra.accum = ctx->d_accum;
+    ra.aov_prim = want_aov ? ctx->d_aov_prim : nullptr;
+    ra.aov_t = want_aov ? ctx->d_aov_t : nullptr;
+    ra.counters = ctx->d_counters;
+    ra.first_frame = first;
+    ra.n_frames = n_frames;
+    ra.frame_stride = ctx->frame_stride;
+    ra.cam = camera_params(ctx->cam);
+    ra.im = image_params(ctx);
+    ra.ip = integrator_params(ctx->cfg);
+    ra.samples_per_pass = (uint32_t)ctx->cfg.samples_per_pass;
+    ra.counting = ctx->counting;
+    std::string err;
+    uint64_t launched = 0;
+    cudaError_t e = ctx->mesh.render(ra, ctx->stream, &launched, &err);
+    if (e != cudaSuccess) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_render(mesh): %s: %s", err.c_str(), cudaGetErrorString(e));
+    ctx->launches += launched;
+  }
+  CU_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  ctx->timing_pending = true;
+  ctx->frame_count += n_frames;
+  return CUDAPT_OK;
+}
+
+int cudapt_synchronize(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return finish_timing(ctx);
+}
+
+int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
+  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_resolve_rgba8: resolution not set");
+  if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "cudapt_resolve_rgba8: no frames rendered yet");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const uint32_t n = ctx->width * ctx->height;
+  CU_TRY(ctx, launch_resolve_rgba8(ctx->d_accum, ctx->d_rgba, n, ctx->frame_count, ctx->stream));
+  ctx->launches += 1;
+  CU_TRY(ctx, cudaMemcpyAsync(ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * (size_t)n);
+  return finish_timing(ctx);
+}
+
+int cudapt_read_accum(cudapt_ctx* ctx, float* host_out, uint32_t* frame_count) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_read_accum: resolution not set");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (host_out)
+    CU_TRY(ctx, cudaMemcpy(host_out, ctx->d_accum, sizeof(float4) * (size_t)ctx->width * ctx->height, cudaMemcpyDeviceToHost));
+  if (frame_count) *frame_count = ctx->frame_count;
+  return finish_timing(ctx);
+}
+
+int cudapt_write_accum(cudapt_ctx* ctx, const float* host_in, uint32_t frame_count) {
+  if (!ctx || !host_in) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_accum: resolution not set");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CU_TRY(ctx, cudaMemcpy(ctx->d_accum, host_in, sizeof(float4) * (size_t)ctx->width * ctx->height, cudaMemcpyHostToDevice));
+  ctx->frame_count = frame_count;
+  return CUDAPT_OK;
+}
+
+int cudapt_read_primary_hits(cudapt_ctx* ctx, uint32_t* prim_id, float* t) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_aov_prim) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_read_primary_hits: resolution not set");
+  if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "cudapt_read_primary_hits: no frames rendered yet");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const size_t n = (size_t)ctx->width * ctx->height;
+  if (prim_id) CU_TRY(ctx, cudaMemcpy(prim_id, ctx->d_aov_prim, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+  if (t) CU_TRY(ctx, cudaMemcpy(t, ctx->d_aov_t, sizeof(float) * n, cudaMemcpyDeviceToHost));
+  return finish_timing(ctx);
+}
+
+int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out) {
+  if (!ctx || !out) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  int rc = finish_timing(ctx);
+  if (rc) return rc;
+  unsigned long long c[kCntSlots];
+  CU_TRY(ctx, cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+  std::memset(out, 0, sizeof(*out));
+  out->paths = c[kCntPaths];
+  out->rays = c[kCntRays];
+  out->nodes_visited = c[kCntNodes];
+  out->tris_tested = c[kCntTris];
+  out->shade_invocations = c[kCntShades];
+  out->kernel_launches = ctx->launches;
+  out->render_ms = ctx->render_ms;
+  out->last_render_ms = ctx->last_render_ms;
+  out->accel_build_ms = ctx->mesh.build_ms;
+  out->accel_bytes = ctx->mesh.accel_bytes;
+  out->frame_count = ctx->frame_count;
+  out->n_triangles = ctx->mesh.n_triangles();
+  out->n_nodes = ctx->mesh.n_nodes();
+  out->n_spheres = ctx->n_spheres;
+  return CUDAPT_OK;
+}
+
+int cudapt_set_counting(cudapt_ctx* ctx, int enabled) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  ctx->counting = enabled != 0;
+  return CUDAPT_OK;
+}
+
+int cudapt_set_tile_partition(cudapt_ctx* ctx, uint32_t rank, uint32_t world, uint32_t tile_w, uint32_t tile_h) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (world == 0 || rank >= world || tile_w == 0 || tile_h == 0)
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_set_tile_partition: rank %u world %u tile %ux%u", rank, world, tile_w, tile_h);
+  ctx->part_rank = rank;
+  ctx->part_world = world;
+  ctx->tile_w = tile_w;
+  ctx->tile_h = tile_h;
+  ctx->mesh.invalidate_image_state();
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  return restart_accumulation(ctx);
+}
+
+int cudapt_set_frame_range(cudapt_ctx* ctx, uint32_t first, uint32_t stride) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (first == 0 || stride == 0) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_set_frame_range: first and stride must be >= 1");
+  ctx->frame_first = first;
+  ctx->frame_stride = stride;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  return restart_accumulation(ctx);
+}
+
+void* cudapt_accum_device_ptr(cudapt_ctx* ctx) { return ctx ? (void*)ctx->d_accum : nullptr; }
+void* cudapt_stream(cudapt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int cudapt_set_frame_count(cudapt_ctx* ctx, uint32_t frame_count) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  ctx->frame_count = frame_count;
+  return CUDAPT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,145 @@
+// Device-side building blocks shared by the sphere megakernel and the mesh wavefront kernels.
+//
+// Numerics contract: this translation unit set is compiled with -fmad=false -prec-div=true
+// -prec-sqrt=true -ftz=false, so every + - * / sqrtf below is one correctly rounded IEEE-754 binary32
+// operation, in the order written.  That order follows the reference
+// (libs/render/src/engines/pathtracer/backends/cpu/CPUPathTracer.cpp, "CPT.cpp") and glm's scalar
+// definitions, which is what makes the accumulation buffer bit-comparable with the CPU path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cudapt {
+
+struct f3 {
+  float x, y, z;
+};
+__host__ __device__ __forceinline__ f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ f3 operator/(f3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
+// glm::dot(vec3) = (x*x' + y*y') + z*z'
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+// glm::cross
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+  return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+// glm::normalize = v * (1 / sqrt(dot(v, v)))
+__device__ __forceinline__ f3 normalize3(f3 a) { return a * (1.0f / sqrtf(dot3(a, a))); }
+__device__ __forceinline__ float max3(f3 a) { return fmaxf(fmaxf(a.x, a.y), a.z); }
+
+// ---- RNG -------------------------------------------------------------------------------------------
+// CPT.cpp:192-195
+__device__ __forceinline__ uint32_t pcg_seed(uint32_t x, uint32_t y, uint32_t width, uint32_t frame) {
+  return x + y * width + frame * 982451653u;
+}
+// CPT.cpp:294-301.  float(w)/4294967295.0f: the divisor is 2^32 in binary32, so the quotient equals
+// RN(float(w)) * 2^-32 exactly (a power-of-two scale), range [0, 1] inclusive.
+__device__ __forceinline__ float pcg_next(uint32_t& state) {
+  state = state * 747796405u + 2891336453u;
+  uint32_t w = ((state >> ((state >> 28) + 4u)) ^ state) * 277803737u;
+  w = (w >> 22) ^ w;
+  return __uint2float_rn(w) * 0x1p-32f;
+}
+
+// Philox4x32-10 keyed (0xB200CAFE, seed), counter (pixel, sample, bounce, block).
+struct rand4 {
+  float u0, u1, u2, u3;
+};
+__device__ __forceinline__ float u01(uint32_t w) { return __uint2float_rn(w >> 8) * 0x1p-24f; }
+__device__ __forceinline__ rand4 philox_block(uint32_t pixel, uint32_t sample, uint32_t bounce, uint32_t block,
+                                              uint32_t seed) {
+  uint32_t c0 = pixel, c1 = sample, c2 = bounce, c3 = block;
+  uint32_t k0 = 0xB200CAFEu, k1 = seed;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0, c1 = lo1, c2 = n2, c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return rand4{u01(c0), u01(c1), u01(c2), u01(c3)};
+}
+
+// cos/sin(2*pi*u), u in [0,1]: quadrant split + Taylor/Horner with separate mul and add (DESIGN.md,
+// "Mesh integrator numerics"); only + - * so CPU and GPU agree bit-for-bit.
+__device__ __forceinline__ void sincos2pi(float u, float& c, float& s) {
+  const float x = u * 4.0f;
+  int q = (int)x;
+  if (q > 3) q = 3;
+  const float f = x - (float)q;
+  const float a = f * 1.57079637f;
+  const float a2 = a * a;
+  float ps = -2.50521084e-08f;
+  ps = ps * a2 + 2.75573192e-06f;
+  ps = ps * a2 + -1.98412701e-04f;
+  ps = ps * a2 + 8.33333377e-03f;
+  ps = ps * a2 + -1.66666672e-01f;
+  ps = ps * a2 + 1.0f;
+  const float sn = ps * a;
+  float pc = 2.08767570e-09f;
+  pc = pc * a2 + -2.75573192e-07f;
+  pc = pc * a2 + 2.48015876e-05f;
+  pc = pc * a2 + -1.38888892e-03f;
+  pc = pc * a2 + 4.16666679e-02f;
+  pc = pc * a2 + -0.5f;
+  const float cs = pc * a2 + 1.0f;
+  c = (q == 0) ? cs : (q == 1) ? -sn : (q == 2) ? -cs : sn;
+  s = (q == 0) ? sn : (q == 1) ? cs : (q == 2) ? -sn : -cs;
+}
+
+// ---- camera / sky ----------------------------------------------------------------------------------
+struct CameraParams {
+  f3 origin, right, up, forward;
+  float tan_half_fov;
+};
+struct ImageParams {
+  uint32_t width, height;
+  float inv_width, inv_height, aspect;  // 1.0f/W, 1.0f/H, (float)W/(float)H  (CPT.cpp:53-54,65)
+  // interleaved-tile partition (cudapt_set_tile_partition); world == 1 disables
+  uint32_t part_rank, part_world, tile_w, tile_h, tiles_x;
+};
+// CPT.cpp:62-73; (jx, jy) = sub-pixel offset, 0 = the reference's pixel-corner sampling.
+__device__ __forceinline__ f3 primary_dir(const CameraParams& cam, const ImageParams& im, uint32_t x, uint32_t y,
+                                          float jx, float jy) {
+  const float u = ((float)x + jx) * im.inv_width;
+  const float v = 1.0f - ((float)y + jy) * im.inv_height;
+  const float uv_x = ((u * 2.0f - 1.0f) * im.aspect) * cam.tan_half_fov;
+  const float uv_y = (v * 2.0f - 1.0f) * cam.tan_half_fov;
+  const float len = sqrtf(uv_x * uv_x + uv_y * uv_y + 1.0f);
+  const float cx = uv_x / len, cy = uv_y / len, cz = 1.0f / len;
+  return mk3((cx * cam.right.x + cy * cam.up.x) + cz * cam.forward.x,
+             (cx * cam.right.y + cy * cam.up.y) + cz * cam.forward.y,
+             (cx * cam.right.z + cy * cam.up.z) + cz * cam.forward.z);
+}
+// CPT.cpp:286-292; glm::mix(x, y, a) = x*(1-a) + y*a
+__device__ __forceinline__ f3 sample_sky(f3 d) {
+  const float t = 0.5f * (d.y + 1.0f);
+  const float omt = 1.0f - t;
+  return mk3(1.0f * omt + 0.5f * t, 1.0f * omt + 0.7f * t, 1.0f * omt + 1.0f * t);
+}
+__device__ __forceinline__ bool owns_pixel(const ImageParams& im, uint32_t x, uint32_t y) {
+  if (im.part_world <= 1u) return true;
+  const uint32_t tx = x / im.tile_w, ty = y / im.tile_h;
+  return (ty * im.tiles_x + tx + ty) % im.part_world == im.part_rank;
+}
+
+struct IntegratorParams {
+  int32_t rng_mode, max_bounces, rr_start, jitter, nee;
+  float tnear, eps, albedo, sky_scale;
+  uint32_t seed;
+};
+
+__device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) {
+  // values are small per thread; sum in 32 bit across the warp
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace cudapt
