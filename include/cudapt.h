@@ -87,7 +87,7 @@ typedef struct cudapt_stats {
   uint64_t nodes_visited;    /* BVH nodes fetched   (only while cudapt_set_counting(ctx,1)) */
   uint64_t tris_tested;      /* triangles tested    (only while cudapt_set_counting(ctx,1)) */
   uint64_t shade_invocations;/* surface interactions shaded */
-  uint64_t kernel_launches;  /* kernels launched by this library since the last reset */
+  uint64_t kernel_launches;  /* kernels launched by this library since cudapt_create (monotonic) */
   double render_ms;          /* CUDA-event time of all cudapt_render() calls since the last reset */
   double last_render_ms;     /* CUDA-event time of the most recent cudapt_render() call */
   double accel_build_ms;     /* host wall time of the last cudapt_build_accel() */
@@ -127,6 +127,11 @@ int cudapt_upload_mesh(cudapt_ctx* ctx, const float* vertices, uint32_t nv, cons
 int cudapt_upload_materials(cudapt_ctx* ctx, const cudapt_material* materials, uint32_t n);
 /* Builds the 8-wide quantised BVH on the host (SAH) and uploads it; replaces rtcCommitScene (CPT.cpp:403). */
 int cudapt_build_accel(cudapt_ctx* ctx);
+/* Copies the already built scene (BVH nodes, packed triangles, materials, light list) from the library's
+ * pinned host staging to the device again and restarts accumulation -- the per-frame cost of a scene that
+ * changed on the host without changing topology (the reference re-commits its Embree scene whenever
+ * Scene::hasChanges(), CPT.cpp:122-131,156-160). */
+int cudapt_reupload_scene(cudapt_ctx* ctx);
 
 /* ---- progressive rendering: render(), CPT.cpp:43-85 ------------------------------------------------ */
 /* Zero the accumulation buffer, frame count = 0 (CPT.cpp:151-154). */

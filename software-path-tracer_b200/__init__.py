@@ -61,6 +61,7 @@ EXPORTS = [
     "cudapt_default_config", "cudapt_default_camera", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
+    "cudapt_reupload_scene",
     "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
@@ -97,6 +98,7 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_upload_mesh.argtypes = [vp, vp, u32, vp, u32, vp]
     lib.cudapt_upload_materials.argtypes = [vp, vp, u32]
     lib.cudapt_build_accel.argtypes = [vp]
+    lib.cudapt_reupload_scene.argtypes = [vp]
     lib.cudapt_reset.argtypes = [vp]
     lib.cudapt_render.argtypes = [vp, u32]
     lib.cudapt_synchronize.argtypes = [vp]
@@ -208,6 +210,9 @@ class PathTracer:
 
     def build_accel(self):
         self._chk(self._lib.cudapt_build_accel(self._h))
+
+    def reupload_scene(self):
+        self._chk(self._lib.cudapt_reupload_scene(self._h))
 
     # rendering
     def reset(self):

@@ -332,13 +332,21 @@ int cudapt_build_accel(cudapt_ctx* ctx) {
   return restart_accumulation(ctx);
 }
 
+int cudapt_reupload_scene(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_reupload_scene: no built mesh scene");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  std::string err;
+  if (!ctx->mesh.reupload(ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_reupload_scene: %s", err.c_str());
+  return restart_accumulation(ctx);
+}
+
 int cudapt_reset(cudapt_ctx* ctx) {
   if (!ctx) return CUDAPT_ERR_INVALID;
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   int rc = finish_timing(ctx);
   if (rc) return rc;
   CU_TRY(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long) * kCntSlots, ctx->stream));
-  ctx->launches = 0;
   ctx->render_ms = 0.0;
   ctx->last_render_ms = 0.0;
   return restart_accumulation(ctx);

@@ -1,0 +1,189 @@
+// Stack-based traversal of the 8-wide quantised BVH (bvh8.h) + the triangle test.  Written
+// __host__ __device__ so that tests/cpp/bvh8_check.cu can run the very same code on the CPU against a
+// brute-force search (that host build is test scaffolding only; the product calls it from CUDA kernels).
+//
+// Exactness: the triangle test is Moller-Trumbore on the stored (v0, e1, e2) record in a FIXED operation
+// order (no FMA: the TU is compiled with -fmad=false), so t is bit-identical to the CPU oracle's.  The
+// closest hit is "smallest t >= tnear, ties to the smallest caller triangle index", which does not depend
+// on traversal order.  Box tests only have to be conservative; they use explicit fmaf and a widened exit
+// distance.
+#pragma once
+#include "common.cuh"
+
+namespace cudapt {
+
+#ifdef __CUDA_ARCH__
+#define PT_LDG4(ptr) __ldg(reinterpret_cast<const uint4*>(ptr))
+#define PT_LDGF4(ptr) __ldg(reinterpret_cast<const float4*>(ptr))
+__device__ __forceinline__ float pt_as_float(uint32_t u) { return __uint_as_float(u); }
+__device__ __forceinline__ uint32_t pt_as_uint(float f) { return __float_as_uint(f); }
+__device__ __forceinline__ int pt_bfind(uint32_t x) { return 31 - __clz(x); }
+__device__ __forceinline__ int pt_popc(uint32_t x) { return __popc(x); }
+#else
+#define PT_LDG4(ptr) (*reinterpret_cast<const uint4*>(ptr))
+#define PT_LDGF4(ptr) (*reinterpret_cast<const float4*>(ptr))
+inline float pt_as_float(uint32_t u) {
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+inline uint32_t pt_as_uint(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+}
+inline int pt_bfind(uint32_t x) { return 31 - __builtin_clz(x); }
+inline int pt_popc(uint32_t x) { return __builtin_popcount(x); }
+#endif
+
+struct TraceHit {
+  float t;        // +inf = miss
+  uint32_t tri;   // leaf-order triangle index, 0xFFFFFFFF = miss
+  uint32_t prim;  // caller's triangle index (tie-break key)
+};
+
+struct RayPre {
+  f3 o, d, idir;
+  uint32_t octinv;  // 7 ^ (direction sign octant)
+};
+
+__host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d) {
+  RayPre r;
+  r.o = o;
+  r.d = d;
+  const float kTiny = 1e-20f;
+  const float dx = fabsf(d.x) < kTiny ? copysignf(kTiny, d.x) : d.x;
+  const float dy = fabsf(d.y) < kTiny ? copysignf(kTiny, d.y) : d.y;
+  const float dz = fabsf(d.z) < kTiny ? copysignf(kTiny, d.z) : d.z;
+  r.idir = mk3(1.0f / dx, 1.0f / dy, 1.0f / dz);
+  const uint32_t oct = (dx < 0.f ? 1u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 4u : 0u);
+  r.octinv = 7u ^ oct;
+  return r;
+}
+
+// Moller-Trumbore, two-sided, fixed operation order (== oracle/twin tri_hit).
+__host__ __device__ __forceinline__ bool tri_test(f3 v0, f3 e1, f3 e2, f3 o, f3 d, float& t) {
+  const f3 pv = cross3(d, e2);
+  const float det = dot3(e1, pv);
+  if (det == 0.0f) return false;
+  const float inv = 1.0f / det;
+  const f3 tv = o - v0;
+  const float u = dot3(tv, pv) * inv;
+  if (!(u >= 0.0f && u <= 1.0f)) return false;
+  const f3 qv = cross3(tv, e1);
+  const float v = dot3(d, qv) * inv;
+  if (!(v >= 0.0f && (u + v) <= 1.0f)) return false;
+  t = dot3(e2, qv) * inv;
+  return true;
+}
+
+// Tests the 8 quantised child boxes of one node; returns the hit mask: bits 24..31 = internal children by
+// traversal priority (slot ^ octinv), bits 0..23 = triangles (offset from tri_base).
+__host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, const uint4 w1, const uint4 w2, const uint4 w3,
+                                                            const uint4 w4, const RayPre& r, float tmin, float tmax) {
+  const float px = pt_as_float(w0.x), py = pt_as_float(w0.y), pz = pt_as_float(w0.z);
+  const uint32_t ew = w0.w;
+  const float adjx = pt_as_float((ew & 0xFFu) << 23) * r.idir.x;
+  const float adjy = pt_as_float(((ew >> 8) & 0xFFu) << 23) * r.idir.y;
+  const float adjz = pt_as_float(((ew >> 16) & 0xFFu) << 23) * r.idir.z;
+  const float orgx = (px - r.o.x) * r.idir.x;
+  const float orgy = (py - r.o.y) * r.idir.y;
+  const float orgz = (pz - r.o.z) * r.idir.z;
+  const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
+  // widened exit so rounding in the slab arithmetic can never cull a box the exact test would enter
+  const float tmax_w = tmax * 1.000001f;
+  const uint32_t octinv4 = r.octinv * 0x01010101u;
+  uint32_t hitmask = 0;
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const uint32_t meta4 = half ? w1.w : w1.z;
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xFFu;
+    const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+    const uint32_t lox = half ? w2.y : w2.x, loy = half ? w2.w : w2.z, loz = half ? w3.y : w3.x;
+    const uint32_t hix = half ? w3.w : w3.z, hiy = half ? w4.y : w4.x, hiz = half ? w4.w : w4.z;
+    const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
+    const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
+    const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int sh = 8 * j;
+      const float t0x = fmaf((float)((nearx >> sh) & 0xFFu), adjx, orgx);
+      const float t0y = fmaf((float)((neary >> sh) & 0xFFu), adjy, orgy);
+      const float t0z = fmaf((float)((nearz >> sh) & 0xFFu), adjz, orgz);
+      const float t1x = fmaf((float)((farx >> sh) & 0xFFu), adjx, orgx);
+      const float t1y = fmaf((float)((fary >> sh) & 0xFFu), adjy, orgy);
+      const float t1z = fmaf((float)((farz >> sh) & 0xFFu), adjz, orgz);
+      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));
+      // an empty slot has child_bits 0; an inverted (255 > 0) box can still pass for a negative direction,
+      // child_bits keeps it out of the mask
+      if (cmin <= cmax * 1.000001f) hitmask |= ((child_bits4 >> sh) & 0xFFu) << ((bit_index4 >> sh) & 0xFFu);
+    }
+  }
+  return hitmask;
+}
+
+// Stack concept: void push(uint2), uint2 pop(), bool empty().
+//
+// kAnyHit = false: closest hit in [tnear, tmax).  kAnyHit = true: returns at the first triangle with
+// tnear <= t < tmax (hit.tri != ~0u means occluded).
+template <bool kAnyHit, bool kCount, class Stack>
+__host__ __device__ __forceinline__ void bvh8_trace(const uint4* __restrict__ nodes, const float4* __restrict__ tris,
+                                                    const RayPre& r, float tnear, float tmax, Stack& stack, TraceHit& hit,
+                                                    uint32_t& n_nodes, uint32_t& n_tris) {
+  hit.t = tmax;
+  hit.tri = 0xFFFFFFFFu;
+  hit.prim = 0xFFFFFFFFu;
+  // slabs are entered slightly early so hits at exactly tnear are never culled by box rounding
+  const float tmin_box = tnear * 0.5f;
+  uint2 ngroup = make_uint2(0u, 0x80000000u);  // the root, as "slot 7^octinv of a virtual parent"
+  for (;;) {
+    if (ngroup.y > 0x00FFFFFFu) {
+      const int bit = pt_bfind(ngroup.y);
+      ngroup.y &= ~(1u << bit);
+      const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
+      if (ngroup.y > 0x00FFFFFFu) stack.push(ngroup);
+      const uint32_t slot = ((uint32_t)bit - 24u) ^ r.octinv;
+      const uint32_t rel = (uint32_t)pt_popc(imask & ~(0xFFFFFFFFu << slot));
+      const uint4* np = nodes + 5 * (size_t)(base + rel);
+      const uint4 w0 = PT_LDG4(np + 0), w1 = PT_LDG4(np + 1), w2 = PT_LDG4(np + 2), w3 = PT_LDG4(np + 3),
+                  w4 = PT_LDG4(np + 4);
+      if (kCount) ++n_nodes;
+      const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, hit.t);
+      ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+      uint32_t tmask = hm & 0x00FFFFFFu;
+      const uint32_t tri_base = w1.y;
+      while (tmask) {
+        const int ti = pt_bfind(tmask);
+        tmask &= ~(1u << ti);
+        const uint32_t tri = tri_base + (uint32_t)ti;
+        const float4* tp = tris + 3 * (size_t)tri;
+        const float4 a = PT_LDGF4(tp + 0), b = PT_LDGF4(tp + 1), c = PT_LDGF4(tp + 2);
+        if (kCount) ++n_tris;
+        float t;
+        if (!tri_test(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), r.o, r.d, t)) continue;
+        if (!(t >= tnear)) continue;
+        const uint32_t prim = pt_as_uint(a.w);
+        if (kAnyHit) {
+          if (t < tmax) {
+            hit.t = t;
+            hit.tri = tri;
+            hit.prim = prim;
+            return;
+          }
+        } else if (t < hit.t || (t == hit.t && prim < hit.prim)) {
+          hit.t = t;
+          hit.tri = tri;
+          hit.prim = prim;
+        }
+      }
+    } else {
+      if (stack.empty()) return;
+      ngroup = stack.pop();
+    }
+  }
+}
+
+}  // namespace cudapt

@@ -1,0 +1,356 @@
+// Host builder of the 8-wide quantised BVH (format: bvh8.h).  Not on the per-frame path: the reference
+// builds its Embree scene once per backend lifetime (CPT.cpp:156-160, :403); build time is reported
+// separately in cudapt_stats.accel_build_ms.
+//
+//   1. binned-SAH binary BVH (16 bins x 3 axes, leaves <= 3 triangles), subtrees built by std::threads;
+//   2. collapse to <= 8 children per node by repeatedly opening the child with the largest surface area;
+//   3. octant-ordered slot assignment (greedy minimum of dot(child centre - node centre, sign_slot));
+//   4. outward-rounded 8-bit quantisation of the child boxes against a per-node power-of-two grid;
+//   5. breadth-first emission: internal children of a node are contiguous (indexable by popcount of
+//      imask), leaf triangles of a node are contiguous (indexable by a 5-bit offset).
+#include "bvh8.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <deque>
+#include <limits>
+#include <thread>
+
+namespace cudapt {
+namespace {
+
+constexpr int kBins = 16;
+constexpr float kInf = std::numeric_limits<float>::infinity();
+
+struct Box {
+  float lo[3] = {kInf, kInf, kInf};
+  float hi[3] = {-kInf, -kInf, -kInf};
+  void grow(const float* l, const float* h) {
+    for (int k = 0; k < 3; ++k) {
+      lo[k] = std::min(lo[k], l[k]);
+      hi[k] = std::max(hi[k], h[k]);
+    }
+  }
+  void grow(const Box& b) { grow(b.lo, b.hi); }
+  float area() const {
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    if (!(dx >= 0.f)) return 0.f;
+    return 2.0f * (dx * dy + dy * dz + dz * dx);
+  }
+};
+
+struct Node2 {
+  Box box;
+  uint32_t left = 0, right = 0;   // children (internal)
+  uint32_t first = 0, count = 0;  // leaf: range in the permutation
+};
+
+struct Builder {
+  const float* blo;
+  const float* bhi;
+  const float* cen;
+  std::vector<uint32_t> perm;
+  std::vector<Node2> nodes;
+  std::atomic<uint32_t> next{1};
+  std::atomic<int> spare{0};
+
+  void build(uint32_t node, uint32_t begin, uint32_t end) {
+    Box box, cbox;
+    for (uint32_t i = begin; i < end; ++i) {
+      const size_t p = perm[i];
+      box.grow(blo + 3 * p, bhi + 3 * p);
+      cbox.grow(cen + 3 * p, cen + 3 * p);
+    }
+    nodes[node].box = box;
+    const uint32_t count = end - begin;
+    auto make_leaf = [&]() {
+      nodes[node].first = begin;
+      nodes[node].count = count;
+    };
+    if (count == 1) return make_leaf();
+
+    // binned SAH over the three axes
+    float best_cost = kInf;
+    int best_axis = -1, best_bin = -1;
+    for (int axis = 0; axis < 3; ++axis) {
+      const float ext = cbox.hi[axis] - cbox.lo[axis];
+      if (!(ext > 0.f)) continue;
+      const float scale = (float)kBins / ext;
+      Box bb[kBins];
+      uint32_t bc[kBins] = {0};
+      for (uint32_t i = begin; i < end; ++i) {
+        const size_t p = perm[i];
+        int k = (int)((cen[3 * p + axis] - cbox.lo[axis]) * scale);
+        k = std::min(std::max(k, 0), kBins - 1);
+        bb[k].grow(blo + 3 * p, bhi + 3 * p);
+        bc[k]++;
+      }
+      float right_area[kBins];
+      uint32_t right_cnt[kBins];
+      Box acc;
+      uint32_t n = 0;
+      for (int k = kBins - 1; k > 0; --k) {
+        acc.grow(bb[k]);
+        n += bc[k];
+        right_area[k] = acc.area();
+        right_cnt[k] = n;
+      }
+      acc = Box();
+      n = 0;
+      for (int k = 0; k < kBins - 1; ++k) {
+        acc.grow(bb[k]);
+        n += bc[k];
+        if (n == 0 || right_cnt[k + 1] == 0) continue;
+        const float c = acc.area() * (float)n + right_area[k + 1] * (float)right_cnt[k + 1];
+        if (c < best_cost) best_cost = c, best_axis = axis, best_bin = k;
+      }
+    }
+    uint32_t mid;
+    if (best_axis < 0) {
+      if (count <= 3) return make_leaf();
+      mid = begin + count / 2;  // coincident centroids: split the index range
+    } else {
+      const float split_cost = 0.8f + best_cost / std::max(box.area(), 1e-30f);
+      if (count <= 3 && split_cost >= (float)count) return make_leaf();
+      const float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
+      const float scale = (float)kBins / ext;
+      const float lo = cbox.lo[best_axis];
+      auto it = std::partition(perm.begin() + begin, perm.begin() + end, [&](uint32_t p) {
+        int k = (int)((cen[3 * (size_t)p + best_axis] - lo) * scale);
+        k = std::min(std::max(k, 0), kBins - 1);
+        return k <= best_bin;
+      });
+      mid = (uint32_t)(it - perm.begin());
+      if (mid == begin || mid == end) mid = begin + count / 2;
+    }
+    const uint32_t l = next.fetch_add(2);
+    nodes[node].left = l;
+    nodes[node].right = l + 1;
+    nodes[node].count = 0;
+    if (count > 32768 && spare.fetch_sub(1) > 0) {
+      std::thread t([this, l, begin, mid]() { build(l, begin, mid); });
+      build(l + 1, mid, end);
+      t.join();
+      spare.fetch_add(1);
+    } else {
+      if (count > 32768) spare.fetch_add(1);  // undo the failed reservation
+      build(l, begin, mid);
+      build(l + 1, mid, end);
+    }
+  }
+};
+
+struct Child {
+  uint32_t node2;
+  Box box;
+  bool leaf;
+};
+
+}  // namespace
+
+bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, const uint32_t* material_id,
+                int threads, Bvh8* out, std::string* err) {
+  (void)nv;
+  if (nt == 0) {
+    *err = "empty mesh";
+    return false;
+  }
+  // ---- packed triangles (caller order) and their boxes ------------------------------------------------
+  std::vector<PackedTri> tri(nt);
+  std::vector<float> blo(3 * (size_t)nt), bhi(3 * (size_t)nt), cen(3 * (size_t)nt);
+  for (uint32_t i = 0; i < nt; ++i) {
+    const float* a = vertices + 3 * (size_t)indices[3 * (size_t)i + 0];
+    const float* b = vertices + 3 * (size_t)indices[3 * (size_t)i + 1];
+    const float* c = vertices + 3 * (size_t)indices[3 * (size_t)i + 2];
+    PackedTri& T = tri[i];
+    for (int k = 0; k < 3; ++k) {
+      T.v0[k] = a[k];
+      T.e1[k] = b[k] - a[k];  // single rounding; the kernels (and the CPU oracle) intersect (v0, e1, e2)
+      T.e2[k] = c[k] - a[k];
+      // box of the triangle the kernels actually see: v0, v0+e1, v0+e2 (+ the caller's vertices), padded
+      const float b2 = a[k] + T.e1[k], c2 = a[k] + T.e2[k];
+      float lo = std::min(std::min(a[k], b[k]), std::min(c[k], std::min(b2, c2)));
+      float hi = std::max(std::max(a[k], b[k]), std::max(c[k], std::max(b2, c2)));
+      const float pad = 4e-7f * std::max(std::fabs(lo), std::fabs(hi)) + 1e-30f;
+      lo -= pad;
+      hi += pad;
+      blo[3 * (size_t)i + k] = lo;
+      bhi[3 * (size_t)i + k] = hi;
+      cen[3 * (size_t)i + k] = 0.5f * lo + 0.5f * hi;
+    }
+    T.prim = i;
+    T.material = material_id ? material_id[i] : 0u;
+    T.pad = 0;
+  }
+  // ---- 1. binary SAH BVH -------------------------------------------------------------------------------
+  Builder B;
+  B.blo = blo.data();
+  B.bhi = bhi.data();
+  B.cen = cen.data();
+  B.perm.resize(nt);
+  for (uint32_t i = 0; i < nt; ++i) B.perm[i] = i;
+  B.nodes.resize(2 * (size_t)nt + 1);
+  B.spare.store(std::max(threads, 1) - 1);
+  B.build(0, 0, nt);
+  const std::vector<Node2>& n2 = B.nodes;
+
+  // ---- 2-5. collapse, order, quantise, emit breadth-first ---------------------------------------------
+  out->nodes.clear();
+  out->tris.clear();
+  out->tris.reserve(nt);
+  out->tri_of_prim.assign(nt, 0u);
+  out->max_depth = 0;
+  out->sah_cost = 0.0;
+  for (int k = 0; k < 3; ++k) out->world_lo[k] = n2[0].box.lo[k], out->world_hi[k] = n2[0].box.hi[k];
+  const double root_area = std::max((double)n2[0].box.area(), 1e-30);
+
+  struct Work {
+    uint32_t node2, node8, depth;
+  };
+  std::deque<Work> queue;
+  out->nodes.emplace_back();
+  queue.push_back({0u, 0u, 1u});
+  while (!queue.empty()) {
+    const Work w = queue.front();
+    queue.pop_front();
+    out->max_depth = std::max(out->max_depth, w.depth);
+    std::vector<Child> ch;
+    if (n2[w.node2].count) {
+      ch.push_back({w.node2, n2[w.node2].box, true});  // whole scene is one leaf
+    } else {
+      ch.push_back({n2[w.node2].left, n2[n2[w.node2].left].box, n2[n2[w.node2].left].count != 0});
+      ch.push_back({n2[w.node2].right, n2[n2[w.node2].right].box, n2[n2[w.node2].right].count != 0});
+      while (ch.size() < 8) {
+        int pick = -1;
+        float pa = -1.f;
+        for (int i = 0; i < (int)ch.size(); ++i)
+          if (!ch[i].leaf && ch[i].box.area() > pa) pa = ch[i].box.area(), pick = i;
+        if (pick < 0) break;
+        const Node2& o = n2[ch[pick].node2];
+        ch[pick] = {o.left, n2[o.left].box, n2[o.left].count != 0};
+        ch.push_back({o.right, n2[o.right].box, n2[o.right].count != 0});
+      }
+    }
+    const int nc = (int)ch.size();
+    Box nb;
+    for (const Child& c : ch) nb.grow(c.box);
+    out->sah_cost += (double)nb.area() / root_area;
+
+    // 3. greedy octant assignment
+    int slot_of[8], child_in_slot[8];
+    std::fill(slot_of, slot_of + 8, -1);
+    std::fill(child_in_slot, child_in_slot + 8, -1);
+    float cost[8][8];
+    for (int s = 0; s < 8; ++s) {
+      const float sx = (s & 1) ? -1.f : 1.f, sy = (s & 2) ? -1.f : 1.f, sz = (s & 4) ? -1.f : 1.f;
+      for (int i = 0; i < nc; ++i) {
+        const float cx = 0.5f * (ch[i].box.lo[0] + ch[i].box.hi[0]) - 0.5f * (nb.lo[0] + nb.hi[0]);
+        const float cy = 0.5f * (ch[i].box.lo[1] + ch[i].box.hi[1]) - 0.5f * (nb.lo[1] + nb.hi[1]);
+        const float cz = 0.5f * (ch[i].box.lo[2] + ch[i].box.hi[2]) - 0.5f * (nb.lo[2] + nb.hi[2]);
+        cost[s][i] = cx * sx + cy * sy + cz * sz;
+      }
+    }
+    for (int round = 0; round < nc; ++round) {
+      float best = kInf;
+      int bs = -1, bi = -1;
+      for (int s = 0; s < 8; ++s) {
+        if (child_in_slot[s] >= 0) continue;
+        for (int i = 0; i < nc; ++i) {
+          if (slot_of[i] >= 0) continue;
+          if (cost[s][i] < best) best = cost[s][i], bs = s, bi = i;
+        }
+      }
+      slot_of[bi] = bs;
+      child_in_slot[bs] = bi;
+    }
+
+    // 4. quantisation grid
+    Bvh8Node N;
+    std::memset(&N, 0, sizeof(N));
+    int ex[3];
+    for (int k = 0; k < 3; ++k) {
+      N.p[k] = nb.lo[k];
+      const double ext = (double)nb.hi[k] - (double)nb.lo[k];
+      int e = -60;
+      if (ext > 0.0) {
+        int kk;
+        (void)std::frexp(ext / 255.0, &kk);
+        e = kk;
+      }
+      ex[k] = std::min(std::max(e, -125), 126);
+    }
+    uint8_t* qlo[3] = {N.qlo_x, N.qlo_y, N.qlo_z};
+    uint8_t* qhi[3] = {N.qhi_x, N.qhi_y, N.qhi_z};
+    for (int k = 0; k < 3; ++k) {
+      for (;;) {
+        const double scale = std::ldexp(1.0, ex[k]);
+        bool ok = true;
+        for (int s = 0; s < 8 && ok; ++s) {
+          const int i = child_in_slot[s];
+          if (i < 0) {
+            qlo[k][s] = 255;  // empty slot: inverted box, never hit
+            qhi[k][s] = 0;
+            continue;
+          }
+          double l = std::floor(((double)ch[i].box.lo[k] - (double)N.p[k]) / scale);
+          double h = std::ceil(((double)ch[i].box.hi[k] - (double)N.p[k]) / scale);
+          while ((double)N.p[k] + l * scale > (double)ch[i].box.lo[k]) l -= 1.0;
+          while ((double)N.p[k] + h * scale < (double)ch[i].box.hi[k]) h += 1.0;
+          l = std::max(l, 0.0);
+          if (h > 255.0) {
+            ok = false;
+            break;
+          }
+          qlo[k][s] = (uint8_t)l;
+          qhi[k][s] = (uint8_t)std::max(h, 0.0);
+        }
+        if (ok) break;
+        ++ex[k];
+      }
+      N.e[k] = (uint8_t)(ex[k] + 127);
+    }
+
+    // 5. emit children in slot order
+    uint32_t n_internal = 0;
+    for (int s = 0; s < 8; ++s)
+      if (child_in_slot[s] >= 0 && !ch[child_in_slot[s]].leaf) ++n_internal;
+    N.child_base = (uint32_t)out->nodes.size();
+    N.tri_base = (uint32_t)out->tris.size();
+    out->nodes.resize(out->nodes.size() + n_internal);
+    uint32_t next_internal = N.child_base, tri_off = 0;
+    for (int s = 0; s < 8; ++s) {
+      const int i = child_in_slot[s];
+      if (i < 0) continue;
+      if (!ch[i].leaf) {
+        N.imask |= (uint8_t)(1u << s);
+        N.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+        queue.push_back({ch[i].node2, next_internal++, w.depth + 1});
+      } else {
+        const Node2& leaf = n2[ch[i].node2];
+        const uint32_t cnt = leaf.count;  // 1..3
+        const uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
+        N.meta[s] = (uint8_t)((unary << 5) | tri_off);
+        for (uint32_t j = 0; j < cnt; ++j) {
+          const uint32_t prim = B.perm[leaf.first + j];
+          out->tri_of_prim[prim] = (uint32_t)out->tris.size();
+          out->tris.push_back(tri[prim]);
+        }
+        tri_off += cnt;
+      }
+    }
+    out->nodes[w.node8] = N;
+  }
+  if (out->max_depth > kBvh8MaxDepth) {
+    *err = "BVH too deep for the traversal stack (" + std::to_string(out->max_depth) + " levels)";
+    return false;
+  }
+  if (out->tris.size() != nt) {
+    *err = "internal error: triangle count mismatch after collapse";
+    return false;
+  }
+  return true;
+}
+
+}  // namespace cudapt

@@ -34,4 +34,61 @@ cudaError_t launch_render_spheres(const SphereLaunch& a, bool philox, cudaStream
 cudaError_t launch_resolve_rgba8(const float4* accum, uint32_t* out, uint32_t n_pixels, uint32_t frame_count,
                                  cudaStream_t stream);
 
+
+// ---- mesh wavefront integrator (wavefront.cu, trace_bvh.cu) -------------------------------------------
+// Path state lives in HBM as structure-of-arrays indexed by PATH ID = sample_in_pass * n_pixels + pixel;
+// queues hold 4-byte path ids, so compaction moves indices only.
+struct WavefrontState {
+  float4* ray_o;        // {o.xyz, tnear}
+  float4* ray_d;        // {d.xyz, tmax}
+  float4* thr;          // {throughput.rgb, bits: bounce count | specular flag << 8}
+  float4* L;            // {radiance.rgb, -}: per-path sum, added to the accumulation buffer in sample order
+  uint2* hit;           // {t bits, leaf-order triangle index (0xFFFFFFFF = miss)}
+  float4* sh_o;         // shadow ray {o.xyz, tmax}
+  float4* sh_d;         // {d.xyz, -}
+  float4* sh_c;         // contribution added to L when unoccluded
+  uint32_t* queue[2];   // ping-pong path queues
+  uint32_t* shadow_queue;
+  uint32_t* counters;   // 4 * (max_bounces + 1) words, zeroed once per pass (see slot helpers below)
+};
+__host__ __device__ inline uint32_t slot_queue_count(uint32_t bounce) { return 4u * bounce + 0u; }
+__host__ __device__ inline uint32_t slot_shadow_count(uint32_t bounce) { return 4u * bounce + 1u; }
+__host__ __device__ inline uint32_t slot_trace_work(uint32_t bounce) { return 4u * bounce + 2u; }
+__host__ __device__ inline uint32_t slot_shadow_work(uint32_t bounce) { return 4u * bounce + 3u; }
+
+struct MeshSceneDevice {
+  const uint4* nodes;        // Bvh8Node as 5 x uint4
+  const float4* tris;        // PackedTri as 3 x float4
+  const float4* materials;   // cudapt_material as 2 x float4
+  const uint32_t* lights;    // leaf-order indices of emissive triangles, ascending caller index
+  uint32_t n_lights;
+  uint32_t n_materials;
+};
+
+struct PassParams {
+  WavefrontState st;
+  MeshSceneDevice scene;
+  CameraParams cam;
+  ImageParams im;
+  IntegratorParams ip;
+  uint32_t n_pixels;
+  uint32_t samples;          // samples of every pixel in this pass
+  uint32_t first_frame;      // global 1-based frame index of sample 0 of this pass
+  uint32_t frame_stride;
+  float4* accum;
+  uint32_t* aov_prim;        // non-null only for the pass that contains the context's first frame
+  float* aov_t;
+  unsigned long long* counters;  // global stats (CounterSlot)
+};
+
+constexpr int kTraceBlock = 128;
+constexpr int kTraceBlocksPerSM = 8;
+constexpr int kShadeBlock = 256;
+
+cudaError_t launch_raygen(const PassParams& p, int sm_count, cudaStream_t s);
+cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count, cudaStream_t s);
+cudaError_t launch_shade(const PassParams& p, uint32_t bounce, int queue_in, int sm_count, cudaStream_t s);
+cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool counting, int sm_count, cudaStream_t s);
+cudaError_t launch_accumulate(const PassParams& p, int sm_count, cudaStream_t s);
+
 }  // namespace cudapt

@@ -1,15 +1,226 @@
+// Host driver of the mesh scene: BVH build + upload, wavefront state, per-pass launch sequence.
 #include "mesh_host.h"
 
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <thread>
+
+#include "bvh8.h"
+
 namespace cudapt {
-struct MeshDevice {};
+
+struct MeshDevice {
+  // scene (pinned host staging kept for re-upload)
+  Bvh8 bvh;
+  std::vector<uint32_t> lights;
+  std::vector<cudapt_material> materials;
+  uint4* d_nodes = nullptr;
+  float4* d_tris = nullptr;
+  float4* d_materials = nullptr;
+  uint32_t* d_lights = nullptr;
+  void* h_pinned = nullptr;  // nodes | tris, pinned, for cudapt_reupload_scene
+  size_t pinned_bytes = 0;
+  // wavefront state
+  WavefrontState st{};
+  uint32_t state_paths = 0;     // capacity in paths
+  uint32_t state_bounces = 0;   // counter slots allocated for this many bounces
+
+  void free_state() {
+    cudaFree(st.ray_o), cudaFree(st.ray_d), cudaFree(st.thr), cudaFree(st.L), cudaFree(st.hit);
+    cudaFree(st.sh_o), cudaFree(st.sh_d), cudaFree(st.sh_c);
+    cudaFree(st.queue[0]), cudaFree(st.queue[1]), cudaFree(st.shadow_queue), cudaFree(st.counters);
+    st = WavefrontState{};
+    state_paths = 0;
+    state_bounces = 0;
+  }
+  void free_scene() {
+    cudaFree(d_nodes), cudaFree(d_tris), cudaFree(d_materials), cudaFree(d_lights);
+    d_nodes = nullptr, d_tris = nullptr, d_materials = nullptr, d_lights = nullptr;
+    if (h_pinned) cudaFreeHost(h_pinned);
+    h_pinned = nullptr;
+    pinned_bytes = 0;
+  }
+};
+
 void MeshScene::set_mesh(const float* v, uint32_t nv, const uint32_t* idx, uint32_t nt, const uint32_t* mid) {
   vertices_.assign(v, v + 3 * (size_t)nv);
   indices_.assign(idx, idx + 3 * (size_t)nt);
-  if (mid) material_id_.assign(mid, mid + nt); else material_id_.assign(nt, 0u);
+  if (mid)
+    material_id_.assign(mid, mid + nt);
+  else
+    material_id_.assign(nt, 0u);
 }
+
 void MeshScene::set_materials(const cudapt_material* m, uint32_t n) { materials_.assign(m, m + n); }
-bool MeshScene::build_and_upload(std::string* err) { *err = "mesh path not built yet"; return false; }
-cudaError_t MeshScene::render(const MeshRenderArgs&, cudaStream_t, uint64_t*, std::string* err) { *err = "mesh path not built yet"; return cudaErrorNotSupported; }
-void MeshScene::invalidate_image_state() {}
-void MeshScene::release() { delete dev_; dev_ = nullptr; }
+
+void MeshScene::invalidate_image_state() {
+  if (dev_) dev_->free_state();
+}
+
+void MeshScene::release() {
+  if (dev_) {
+    dev_->free_state();
+    dev_->free_scene();
+    delete dev_;
+    dev_ = nullptr;
+  }
+}
+
+#define MH_TRY(expr)                                                    \
+  do {                                                                  \
+    cudaError_t e__ = (expr);                                           \
+    if (e__ != cudaSuccess) {                                           \
+      *err = std::string(#expr) + ": " + cudaGetErrorString(e__);       \
+      return false;                                                     \
+    }                                                                   \
+  } while (0)
+
+bool MeshScene::build_and_upload(std::string* err) {
+  const auto t0 = std::chrono::steady_clock::now();
+  if (!dev_) dev_ = new MeshDevice();
+  dev_->free_scene();
+  const uint32_t nt = (uint32_t)(indices_.size() / 3), nv = (uint32_t)(vertices_.size() / 3);
+  std::vector<cudapt_material> mats = materials_;
+  if (mats.empty()) {  // default: the reference's constant 0.7 albedo (CPT.cpp:260) as a Lambert material
+    cudapt_material d;
+    std::memset(&d, 0, sizeof(d));
+    d.albedo[0] = d.albedo[1] = d.albedo[2] = 0.7f;
+    mats.push_back(d);
+  }
+  int threads = (int)std::thread::hardware_concurrency();
+  threads = std::max(1, std::min(threads, 32));
+  if (!build_bvh8(vertices_.data(), nv, indices_.data(), nt, material_id_.data(), threads, &dev_->bvh, err)) return false;
+  const Bvh8& bvh = dev_->bvh;
+  // emissive triangles, ascending caller index (the order the NEE light pick is defined on)
+  dev_->lights.clear();
+  for (uint32_t i = 0; i < nt; ++i) {
+    uint32_t m = material_id_[i];
+    if (m >= mats.size()) m = 0;
+    if (mats[m].emission[0] > 0.f || mats[m].emission[1] > 0.f || mats[m].emission[2] > 0.f)
+      dev_->lights.push_back(bvh.tri_of_prim[i]);
+  }
+  dev_->materials = mats;
+  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
+  MH_TRY(cudaMallocHost(&dev_->h_pinned, nb + tb));
+  dev_->pinned_bytes = nb + tb;
+  std::memcpy(dev_->h_pinned, bvh.nodes.data(), nb);
+  std::memcpy((char*)dev_->h_pinned + nb, bvh.tris.data(), tb);
+  MH_TRY(cudaMalloc(&dev_->d_nodes, nb));
+  MH_TRY(cudaMalloc(&dev_->d_tris, tb));
+  MH_TRY(cudaMalloc(&dev_->d_materials, mats.size() * sizeof(cudapt_material)));
+  MH_TRY(cudaMalloc(&dev_->d_lights, std::max<size_t>(dev_->lights.size(), 1) * sizeof(uint32_t)));
+  n_tris_built_ = nt;
+  n_nodes_built_ = (uint32_t)bvh.nodes.size();
+  accel_bytes = nb + tb;
+  if (!reupload(nullptr, err)) return false;
+  MH_TRY(cudaDeviceSynchronize());
+  build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return true;
+}
+
+bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
+  if (!dev_ || !dev_->h_pinned) {
+    *err = "no built scene";
+    return false;
+  }
+  const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
+  MH_TRY(cudaMemcpyAsync(dev_->d_nodes, dev_->h_pinned, nb, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_tris, (char*)dev_->h_pinned + nb, tb, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_materials, dev_->materials.data(), dev_->materials.size() * sizeof(cudapt_material),
+                         cudaMemcpyHostToDevice, stream));
+  if (!dev_->lights.empty())
+    MH_TRY(cudaMemcpyAsync(dev_->d_lights, dev_->lights.data(), dev_->lights.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                           stream));
+  return true;
+}
+
+static cudaError_t ensure_state(MeshDevice* d, uint32_t paths, uint32_t bounces) {
+  if (d->state_paths >= paths && d->state_bounces >= bounces) return cudaSuccess;
+  d->free_state();
+  WavefrontState& st = d->st;
+  cudaError_t e;
+#define ST_ALLOC(ptr, bytes) \
+  if ((e = cudaMalloc(&ptr, (bytes))) != cudaSuccess) return e
+  ST_ALLOC(st.ray_o, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.ray_d, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.thr, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.L, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.hit, sizeof(uint2) * (size_t)paths);
+  ST_ALLOC(st.sh_o, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.sh_d, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.sh_c, sizeof(float4) * (size_t)paths);
+  ST_ALLOC(st.queue[0], sizeof(uint32_t) * (size_t)paths);
+  ST_ALLOC(st.queue[1], sizeof(uint32_t) * (size_t)paths);
+  ST_ALLOC(st.shadow_queue, sizeof(uint32_t) * (size_t)paths);
+  ST_ALLOC(st.counters, sizeof(uint32_t) * 4 * (size_t)(bounces + 2));
+#undef ST_ALLOC
+  d->state_paths = paths;
+  d->state_bounces = bounces;
+  return cudaSuccess;
+}
+
+cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err) {
+  *launches = 0;
+  if (!dev_ || !dev_->d_nodes) {
+    *err = "accel not built";
+    return cudaErrorInvalidValue;
+  }
+  const uint32_t n_pixels = a.im.width * a.im.height;
+  const uint32_t S = std::max(1u, a.samples_per_pass);
+  const uint32_t max_b = (uint32_t)a.ip.max_bounces;
+  cudaError_t e = ensure_state(dev_, n_pixels * S, max_b);
+  if (e != cudaSuccess) {
+    *err = "wavefront state allocation";
+    return e;
+  }
+  PassParams p;
+  p.st = dev_->st;
+  p.scene.nodes = dev_->d_nodes;
+  p.scene.tris = dev_->d_tris;
+  p.scene.materials = dev_->d_materials;
+  p.scene.lights = dev_->d_lights;
+  p.scene.n_lights = (uint32_t)dev_->lights.size();
+  p.scene.n_materials = (uint32_t)dev_->materials.size();
+  p.cam = a.cam;
+  p.im = a.im;
+  p.ip = a.ip;
+  p.n_pixels = n_pixels;
+  p.frame_stride = a.frame_stride;
+  p.accum = a.accum;
+  p.counters = a.counters;
+  const bool nee = a.ip.nee && p.scene.n_lights > 0;
+#define R_TRY(expr, what)     \
+  if ((e = (expr)) != cudaSuccess) { \
+    *err = what;              \
+    return e;                 \
+  }
+  uint32_t done = 0;
+  while (done < a.n_frames) {
+    const uint32_t s = std::min(S, a.n_frames - done);
+    p.samples = s;
+    p.first_frame = a.first_frame + done * a.frame_stride;
+    p.aov_prim = done == 0 ? a.aov_prim : nullptr;
+    p.aov_t = done == 0 ? a.aov_t : nullptr;
+    R_TRY(cudaMemsetAsync(p.st.counters, 0, sizeof(uint32_t) * 4 * (size_t)(max_b + 2), stream), "counter memset");
+    R_TRY(launch_raygen(p, sm_count, stream), "raygen");
+    ++*launches;
+    for (uint32_t b = 0; b < max_b; ++b) {
+      const int qin = (int)(b & 1u);
+      R_TRY(launch_trace_closest(p, b, qin, a.counting, sm_count, stream), "trace_closest");
+      R_TRY(launch_shade(p, b, qin, sm_count, stream), "shade");
+      *launches += 2;
+      if (nee) {
+        R_TRY(launch_trace_shadow(p, b, a.counting, sm_count, stream), "trace_shadow");
+        ++*launches;
+      }
+    }
+    R_TRY(launch_accumulate(p, sm_count, stream), "accumulate");
+    ++*launches;
+    done += s;
+  }
+#undef R_TRY
+  return cudaSuccess;
+}
+
 }  // namespace cudapt

@@ -35,6 +35,8 @@ class MeshScene {
   void set_materials(const cudapt_material* m, uint32_t n);
   bool has_host_mesh() const { return !indices_.empty(); }
   bool build_and_upload(std::string* err);
+  // H2D copy of the packed scene (nodes, triangles, materials, lights) from pinned host memory.
+  bool reupload(cudaStream_t stream, std::string* err);
   cudaError_t render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err);
   void invalidate_image_state();
   void release();

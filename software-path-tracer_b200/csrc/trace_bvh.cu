@@ -1,0 +1,203 @@
+// K2b / K2c: persistent-thread traversal of the 8-wide quantised BVH (closest hit and any-hit).
+// Replaces rtcIntersect1 (CPT.cpp:227) for triangle scenes.
+//
+// Launch shape: grid = SMs x kTraceBlocksPerSM CTAs of 128 threads, resident for the whole launch.  Each
+// warp pulls rays from the bounce's queue through a global atomic counter (one atomic per refill, issued by
+// lane 0 and broadcast with shfl); lanes whose ray finished are refilled as soon as the number of lanes
+// still traversing together drops below kRefillThreshold (ballot/popc), so a warp keeps > 50 % of its
+// lanes busy until the queue drains.  Traversal stack: 8 entries per thread in shared memory (interleaved
+// by thread id: conflict-free 64-bit accesses), the rest in local memory.  Node and triangle fetches are
+// 128-bit read-only loads (5 per node, 3 per triangle).
+#include "bvh8_traverse.cuh"
+#include "kernels.h"
+
+namespace cudapt {
+namespace {
+
+constexpr int kSharedStack = 8;
+constexpr int kLocalStack = 32;
+constexpr int kRefillThreshold = 20;
+
+struct DeviceStack {
+  uint2* shared_base;  // &smem[threadIdx.x], stride blockDim.x
+  uint2 local[kLocalStack];
+  int sp;
+  __device__ __forceinline__ void push(uint2 v) {
+    if (sp < kSharedStack)
+      shared_base[sp * kTraceBlock] = v;
+    else if (sp < kSharedStack + kLocalStack)
+      local[sp - kSharedStack] = v;
+    ++sp;  // deeper than the builder's kBvh8MaxDepth bound cannot happen
+  }
+  __device__ __forceinline__ uint2 pop() {
+    --sp;
+    return sp < kSharedStack ? shared_base[sp * kTraceBlock] : local[sp - kSharedStack];
+  }
+  __device__ __forceinline__ bool empty() const { return sp == 0; }
+};
+
+// One resumable traversal state per lane.  The generic bvh8_trace() in bvh8_traverse.cuh runs a ray to
+// completion; here the same steps are driven by an outer loop that can interleave refills.
+template <bool kAnyHit, bool kCount>
+__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
+    trace_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
+                 const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
+                 uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
+                 const float4* __restrict__ contrib, unsigned long long* __restrict__ stats) {
+  __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
+  const uint32_t n = *count_ptr;
+  const unsigned lane = threadIdx.x & 31u;
+  DeviceStack stack;
+  stack.shared_base = s_stack + threadIdx.x;
+  stack.sp = 0;
+
+  bool active = false, drained = false;
+  uint32_t path = 0;
+  RayPre r;
+  float tnear = 0.f, tmax = 0.f, tmin_box = 0.f;
+  TraceHit hit;
+  uint2 ngroup = make_uint2(0u, 0u);
+  uint32_t n_nodes = 0, n_tris = 0;
+
+  for (;;) {
+    // ---- refill idle lanes (warp-synchronous) ----
+    const unsigned idle = __ballot_sync(0xffffffffu, !active);
+    if (idle && !drained) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(work_counter, (uint32_t)__popc(idle));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (base >= n) drained = true;
+      if (!active) {
+        const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        if (i < n) {
+          path = queue[i];
+          const float4 o4 = ray_o[path], d4 = ray_d[path];
+          r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+          if (kAnyHit) {
+            tnear = d4.w;  // shadow rays: {o, tmax}, {d, tnear}
+            tmax = o4.w;
+          } else {
+            tnear = o4.w;
+            tmax = d4.w;
+          }
+          tmin_box = tnear * 0.5f;
+          hit.t = tmax;
+          hit.tri = 0xFFFFFFFFu;
+          hit.prim = 0xFFFFFFFFu;
+          ngroup = make_uint2(0u, 0x80000000u);
+          stack.sp = 0;
+          active = true;
+        }
+      }
+    }
+    if (__ballot_sync(0xffffffffu, active) == 0u) break;
+
+    // ---- traverse until this lane finishes or too few lanes are left running together ----
+    if (active) {
+      for (;;) {
+        bool finished = false;
+        if (ngroup.y > 0x00FFFFFFu) {
+          const int bit = pt_bfind(ngroup.y);
+          ngroup.y &= ~(1u << bit);
+          const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
+          if (ngroup.y > 0x00FFFFFFu) stack.push(ngroup);
+          const uint32_t slot = ((uint32_t)bit - 24u) ^ r.octinv;
+          const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+          const uint4* np = nodes + 5 * (size_t)(base + rel);
+          const uint4 w0 = __ldg(np + 0), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+          if (kCount) ++n_nodes;
+          const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, hit.t);
+          ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+          uint32_t tmask = hm & 0x00FFFFFFu;
+          const uint32_t tri_base = w1.y;
+          while (tmask) {
+            const int ti = pt_bfind(tmask);
+            tmask &= ~(1u << ti);
+            const uint32_t tri = tri_base + (uint32_t)ti;
+            const float4* tp = tris + 3 * (size_t)tri;
+            const float4 a = __ldg(tp + 0), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            if (kCount) ++n_tris;
+            float t;
+            if (!tri_test(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), r.o, r.d, t)) continue;
+            if (!(t >= tnear)) continue;
+            const uint32_t prim = __float_as_uint(a.w);
+            if (kAnyHit) {
+              if (t < tmax) {
+                hit.tri = tri;
+                finished = true;
+                break;
+              }
+            } else if (t < hit.t || (t == hit.t && prim < hit.prim)) {
+              hit.t = t;
+              hit.tri = tri;
+              hit.prim = prim;
+            }
+          }
+        } else if (stack.empty()) {
+          finished = true;
+        } else {
+          ngroup = stack.pop();
+        }
+        if (finished) {
+          if (kAnyHit) {
+            if (hit.tri == 0xFFFFFFFFu) {  // unoccluded: add the light sample (path-private slot, no atomics)
+              float4 l = L[path];
+              const float4 c = contrib[path];
+              l.x += c.x;
+              l.y += c.y;
+              l.z += c.z;
+              L[path] = l;
+            }
+          } else {
+            hit_out[path] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
+          }
+          active = false;
+          break;
+        }
+        if (!drained && __popc(__activemask()) < kRefillThreshold) break;
+      }
+    }
+    __syncwarp();
+  }
+  if (kCount) {
+    const uint64_t wn = warp_sum_u32(n_nodes), wt = warp_sum_u32(n_tris);
+    if (lane == 0) {
+      atomicAdd(&stats[kCntNodes], (unsigned long long)wn);
+      atomicAdd(&stats[kCntTris], (unsigned long long)wt);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
+}
+
+}  // namespace
+
+cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count,
+                                 cudaStream_t s) {
+  const dim3 grid(sm_count * kTraceBlocksPerSM), block(kTraceBlock);
+  const WavefrontState& st = p.st;
+  if (counting)
+    trace_kernel<false, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
+                                                      st.counters + slot_queue_count(bounce),
+                                                      st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters);
+  else
+    trace_kernel<false, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
+                                                       st.counters + slot_queue_count(bounce),
+                                                       st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool counting, int sm_count, cudaStream_t s) {
+  const dim3 grid(sm_count * kTraceBlocksPerSM), block(kTraceBlock);
+  const WavefrontState& st = p.st;
+  if (counting)
+    trace_kernel<true, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
+                                                     st.counters + slot_shadow_count(bounce),
+                                                     st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters);
+  else
+    trace_kernel<true, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
+                                                      st.counters + slot_shadow_count(bounce),
+                                                      st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters);
+  return cudaGetLastError();
+}
+
+}  // namespace cudapt
