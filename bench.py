@@ -41,7 +41,7 @@ WORKLOADS = {
                w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=4),
                fov=1.0, kind="mesh"),
 }
-DEFAULT_WORKLOAD = "c1"
+DEFAULT_WORKLOAD = "c3"
 
 
 def load_peaks():
@@ -260,6 +260,14 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    if wl["kind"] == "mesh":
+        # node/triangle visit counts for the roofline, from the instrumented traversal, outside the timed region
+        tr.reset()
+        tr.set_counting(True)
+        tr.render(min(spp, int(wl["cfg"].get("samples_per_pass", 1))))
+        cs = tr.stats()
+        tr._counted = {"nodes_per_ray": cs.nodes_visited / max(cs.rays, 1), "tris_per_ray": cs.tris_tested / max(cs.rays, 1)}
+        tr.set_counting(False)
     for _ in range(args.warmup):
         step()
     sync_all()
