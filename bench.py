@@ -33,12 +33,12 @@ WORKLOADS = {
                w=640, h=360, spp=16, cfg=dict(), fov=1.0, kind="spheres"),
     "c2": dict(desc="configs[1]: Cornell box mesh (diffuse+mirror+dielectric), 1280x720, 256 spp, area-light NEE, depth 8",
                w=1280, h=720, spp=256, cfg=dict(rng_mode=1, max_bounces=8, sky_scale=0.0, jitter=1, nee=1, seed=2,
-                                                samples_per_pass=4), fov=0.36, kind="mesh"),
+                                                samples_per_pass=16), fov=0.36, kind="mesh"),
     "c3": dict(desc="configs[2]: 1,002,528-triangle fBm height field, GGX-coated, 1920x1080, 64 spp, depth 8",
-               w=1920, h=1080, spp=64, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=4),
+               w=1920, h=1080, spp=64, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=16),
                fov=1.0, kind="mesh"),
     "c4": dict(desc="configs[3]: 20,000,002-triangle flattened rock field (BVH > L2), 1920x1080, 128 spp, depth 16",
-               w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=4),
+               w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=16),
                fov=1.0, kind="mesh"),
 }
 DEFAULT_WORKLOAD = "c3"

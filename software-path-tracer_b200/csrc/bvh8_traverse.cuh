@@ -36,6 +36,18 @@ inline int pt_bfind(uint32_t x) { return 31 - __builtin_clz(x); }
 inline int pt_popc(uint32_t x) { return __builtin_popcount(x); }
 #endif
 
+// Byte j of `word` as a float.  On the device: PRMT splices the byte into the mantissa of 2^23 (0x4B000000)
+// and one FADD removes the bias -- two full-rate instructions instead of a shift/mask plus a quarter-rate I2F
+// (48 conversions per node made I2F the busiest pipe of the traversal kernel; profiles/r01_trace_notes.md).
+template <int J>
+__host__ __device__ __forceinline__ float byte_as_float(uint32_t word) {
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + J)) - 8388608.0f;
+#else
+  return (float)((word >> (8 * J)) & 0xFFu);
+#endif
+}
+
 struct TraceHit {
   float t;        // +inf = miss
   uint32_t tri;   // leaf-order triangle index, 0xFFFFFFFF = miss
@@ -91,7 +103,7 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   const float orgz = (pz - r.o.z) * r.idir.z;
   const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
   // widened exit so rounding in the slab arithmetic can never cull a box the exact test would enter
-  const float tmax_w = tmax * 1.000001f;
+  const float tmax_w = tmax * 1.000002f;
   const uint32_t octinv4 = r.octinv * 0x01010101u;
   uint32_t hitmask = 0;
 #pragma unroll
@@ -106,29 +118,78 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
     const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
     const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int sh = 8 * j;
-      const float t0x = fmaf((float)((nearx >> sh) & 0xFFu), adjx, orgx);
-      const float t0y = fmaf((float)((neary >> sh) & 0xFFu), adjy, orgy);
-      const float t0z = fmaf((float)((nearz >> sh) & 0xFFu), adjz, orgz);
-      const float t1x = fmaf((float)((farx >> sh) & 0xFFu), adjx, orgx);
-      const float t1y = fmaf((float)((fary >> sh) & 0xFFu), adjy, orgy);
-      const float t1z = fmaf((float)((farz >> sh) & 0xFFu), adjz, orgz);
-      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
-      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));
-      // an empty slot has child_bits 0; an inverted (255 > 0) box can still pass for a negative direction,
-      // child_bits keeps it out of the mask
-      if (cmin <= cmax * 1.000001f) hitmask |= ((child_bits4 >> sh) & 0xFFu) << ((bit_index4 >> sh) & 0xFFu);
+#define PT_CHILD(J)                                                                                      \
+    {                                                                                                    \
+      const float t0x = fmaf(byte_as_float<J>(nearx), adjx, orgx);                                       \
+      const float t0y = fmaf(byte_as_float<J>(neary), adjy, orgy);                                       \
+      const float t0z = fmaf(byte_as_float<J>(nearz), adjz, orgz);                                       \
+      const float t1x = fmaf(byte_as_float<J>(farx), adjx, orgx);                                        \
+      const float t1y = fmaf(byte_as_float<J>(fary), adjy, orgy);                                        \
+      const float t1z = fmaf(byte_as_float<J>(farz), adjz, orgz);                                        \
+      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                       \
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));                                     \
+      /* an empty slot has child_bits 0, which keeps it out of the mask whatever its box test says */    \
+      if (cmin <= cmax) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
     }
+    PT_CHILD(0) PT_CHILD(1) PT_CHILD(2) PT_CHILD(3)
+#undef PT_CHILD
   }
   return hitmask;
 }
 
 // Stack concept: void push(uint2), uint2 pop(), bool empty().
-//
-// kAnyHit = false: closest hit in [tnear, tmax).  kAnyHit = true: returns at the first triangle with
-// tnear <= t < tmax (hit.tri != ~0u means occluded).
+
+// One traversal step.  Precondition: ngroup has at least one internal child left (ngroup.y > 0x00FFFFFF).
+// Takes the highest-priority child, pushes what is left of the group, fetches that node (5 x LDG.128) and
+// tests its 8 children.  On return ngroup describes the fetched node's internal hits and (tri_base, tmask)
+// its triangle hits.
+template <class Stack>
+__host__ __device__ __forceinline__ void node_step(const uint4* __restrict__ nodes, const RayPre& r, float tmin_box,
+                                                   float tmax, uint2& ngroup, Stack& stack, uint32_t& tri_base,
+                                                   uint32_t& tmask) {
+  const int bit = pt_bfind(ngroup.y);
+  ngroup.y &= ~(1u << bit);
+  const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
+  if (ngroup.y > 0x00FFFFFFu) stack.push(ngroup);
+  const uint32_t slot = ((uint32_t)bit - 24u) ^ r.octinv;
+  const uint32_t rel = (uint32_t)pt_popc(imask & ~(0xFFFFFFFFu << slot));
+  const uint4* np = nodes + 5 * (size_t)(base + rel);
+  const uint4 w0 = PT_LDG4(np + 0), w1 = PT_LDG4(np + 1), w2 = PT_LDG4(np + 2), w3 = PT_LDG4(np + 3), w4 = PT_LDG4(np + 4);
+  const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, tmax);
+  ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+  tri_base = w1.y;
+  tmask = hm & 0x00FFFFFFu;
+}
+
+// Tests triangle `tri`; returns true when an any-hit query is satisfied.  Closest-hit rule: smallest
+// t >= tnear, ties to the smallest caller index.
+template <bool kAnyHit>
+__host__ __device__ __forceinline__ bool tri_step(const float4* __restrict__ tris, uint32_t tri, const RayPre& r, float tnear,
+                                                  float tmax, TraceHit& hit) {
+  const float4* tp = tris + 3 * (size_t)tri;
+  const float4 a = PT_LDGF4(tp + 0), b = PT_LDGF4(tp + 1), c = PT_LDGF4(tp + 2);
+  float t;
+  if (!tri_test(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), r.o, r.d, t)) return false;
+  if (!(t >= tnear)) return false;
+  const uint32_t prim = pt_as_uint(a.w);
+  if (kAnyHit) {
+    if (t < tmax) {
+      hit.t = t;
+      hit.tri = tri;
+      hit.prim = prim;
+      return true;
+    }
+  } else if (t < hit.t || (t == hit.t && prim < hit.prim)) {
+    hit.t = t;
+    hit.tri = tri;
+    hit.prim = prim;
+  }
+  return false;
+}
+
+// Runs one ray to completion (host tests; the CUDA kernels drive node_step/tri_step themselves so they can
+// refill lanes between steps).  kAnyHit = false: closest hit in [tnear, tmax).  kAnyHit = true: returns at the
+// first triangle with tnear <= t < tmax (hit.tri != ~0u means occluded).
 template <bool kAnyHit, bool kCount, class Stack>
 __host__ __device__ __forceinline__ void bvh8_trace(const uint4* __restrict__ nodes, const float4* __restrict__ tris,
                                                     const RayPre& r, float tnear, float tmax, Stack& stack, TraceHit& hit,
@@ -140,46 +201,16 @@ __host__ __device__ __forceinline__ void bvh8_trace(const uint4* __restrict__ no
   const float tmin_box = tnear * 0.5f;
   uint2 ngroup = make_uint2(0u, 0x80000000u);  // the root, as "slot 7^octinv of a virtual parent"
   for (;;) {
-    if (ngroup.y > 0x00FFFFFFu) {
-      const int bit = pt_bfind(ngroup.y);
-      ngroup.y &= ~(1u << bit);
-      const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
-      if (ngroup.y > 0x00FFFFFFu) stack.push(ngroup);
-      const uint32_t slot = ((uint32_t)bit - 24u) ^ r.octinv;
-      const uint32_t rel = (uint32_t)pt_popc(imask & ~(0xFFFFFFFFu << slot));
-      const uint4* np = nodes + 5 * (size_t)(base + rel);
-      const uint4 w0 = PT_LDG4(np + 0), w1 = PT_LDG4(np + 1), w2 = PT_LDG4(np + 2), w3 = PT_LDG4(np + 3),
-                  w4 = PT_LDG4(np + 4);
-      if (kCount) ++n_nodes;
-      const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, hit.t);
-      ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
-      uint32_t tmask = hm & 0x00FFFFFFu;
-      const uint32_t tri_base = w1.y;
-      while (tmask) {
-        const int ti = pt_bfind(tmask);
-        tmask &= ~(1u << ti);
-        const uint32_t tri = tri_base + (uint32_t)ti;
-        const float4* tp = tris + 3 * (size_t)tri;
-        const float4 a = PT_LDGF4(tp + 0), b = PT_LDGF4(tp + 1), c = PT_LDGF4(tp + 2);
-        if (kCount) ++n_tris;
-        float t;
-        if (!tri_test(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), r.o, r.d, t)) continue;
-        if (!(t >= tnear)) continue;
-        const uint32_t prim = pt_as_uint(a.w);
-        if (kAnyHit) {
-          if (t < tmax) {
-            hit.t = t;
-            hit.tri = tri;
-            hit.prim = prim;
-            return;
-          }
-        } else if (t < hit.t || (t == hit.t && prim < hit.prim)) {
-          hit.t = t;
-          hit.tri = tri;
-          hit.prim = prim;
-        }
-      }
-    } else {
+    uint32_t tri_base, tmask;
+    node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tmask);
+    if (kCount) ++n_nodes;
+    while (tmask) {
+      const int ti = pt_bfind(tmask);
+      tmask &= ~(1u << ti);
+      if (kCount) ++n_tris;
+      if (tri_step<kAnyHit>(tris, tri_base + (uint32_t)ti, r, tnear, tmax, hit)) return;
+    }
+    if (ngroup.y <= 0x00FFFFFFu) {
       if (stack.empty()) return;
       ngroup = stack.pop();
     }

@@ -92,51 +92,29 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
     }
     if (__ballot_sync(0xffffffffu, active) == 0u) break;
 
-    // ---- traverse until this lane finishes or too few lanes are left running together ----
-    if (active) {
-      for (;;) {
+    // ---- warp-synchronous traversal: every iteration each active lane does ONE node step (fetch + 8 box
+    // tests), its triangle tests, and a pop if the node had no internal hits; the ballot at the bottom
+    // reconverges the warp, so node steps always execute with all active lanes together ----
+    for (;;) {
+      if (active) {
+        uint32_t tri_base, tmask;
+        node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tmask);
+        if (kCount) ++n_nodes;
         bool finished = false;
-        if (ngroup.y > 0x00FFFFFFu) {
-          const int bit = pt_bfind(ngroup.y);
-          ngroup.y &= ~(1u << bit);
-          const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
-          if (ngroup.y > 0x00FFFFFFu) stack.push(ngroup);
-          const uint32_t slot = ((uint32_t)bit - 24u) ^ r.octinv;
-          const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
-          const uint4* np = nodes + 5 * (size_t)(base + rel);
-          const uint4 w0 = __ldg(np + 0), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
-          if (kCount) ++n_nodes;
-          const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, hit.t);
-          ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
-          uint32_t tmask = hm & 0x00FFFFFFu;
-          const uint32_t tri_base = w1.y;
-          while (tmask) {
-            const int ti = pt_bfind(tmask);
-            tmask &= ~(1u << ti);
-            const uint32_t tri = tri_base + (uint32_t)ti;
-            const float4* tp = tris + 3 * (size_t)tri;
-            const float4 a = __ldg(tp + 0), b = __ldg(tp + 1), c = __ldg(tp + 2);
-            if (kCount) ++n_tris;
-            float t;
-            if (!tri_test(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), r.o, r.d, t)) continue;
-            if (!(t >= tnear)) continue;
-            const uint32_t prim = __float_as_uint(a.w);
-            if (kAnyHit) {
-              if (t < tmax) {
-                hit.tri = tri;
-                finished = true;
-                break;
-              }
-            } else if (t < hit.t || (t == hit.t && prim < hit.prim)) {
-              hit.t = t;
-              hit.tri = tri;
-              hit.prim = prim;
-            }
+        while (tmask) {
+          const int ti = pt_bfind(tmask);
+          tmask &= ~(1u << ti);
+          if (kCount) ++n_tris;
+          if (tri_step<kAnyHit>(tris, tri_base + (uint32_t)ti, r, tnear, tmax, hit)) {
+            finished = true;
+            break;
           }
-        } else if (stack.empty()) {
-          finished = true;
-        } else {
-          ngroup = stack.pop();
+        }
+        if (!finished && ngroup.y <= 0x00FFFFFFu) {
+          if (stack.empty())
+            finished = true;
+          else
+            ngroup = stack.pop();
         }
         if (finished) {
           if (kAnyHit) {
@@ -152,12 +130,12 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
             hit_out[path] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
           }
           active = false;
-          break;
         }
-        if (!drained && __popc(__activemask()) < kRefillThreshold) break;
       }
+      const unsigned act = __ballot_sync(0xffffffffu, active);
+      if (act == 0u) break;
+      if (!drained && __popc(act) < kRefillThreshold) break;
     }
-    __syncwarp();
   }
   if (kCount) {
     const uint64_t wn = warp_sum_u32(n_nodes), wt = warp_sum_u32(n_tris);

@@ -30,6 +30,43 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
   return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
 }
 
+// Block-aggregated append to up to two queues at once: warp ballots -> per-warp counts in shared memory ->
+// ONE atomic per queue per CTA round.  (Per-warp atomics on a single counter serialise in the L2 atomic unit:
+// 260 k same-address atomics per 8.3 M-path pass cost ~0.3 ms; profiles/r01_notes.md.)  Must be called by
+// every thread of the CTA.
+struct BlockAppend {
+  uint32_t slot_a, slot_b;
+};
+__device__ __forceinline__ BlockAppend block_append2(uint32_t* counter_a, bool pred_a, uint32_t* counter_b, bool pred_b) {
+  __shared__ uint32_t s_cnt[2][kShadeBlock / 32];
+  __shared__ uint32_t s_base[2];
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const unsigned ma = __ballot_sync(0xffffffffu, pred_a);
+  const unsigned mb = counter_b ? __ballot_sync(0xffffffffu, pred_b) : 0u;
+  if (lane == 0) {
+    s_cnt[0][warp] = (uint32_t)__popc(ma);
+    s_cnt[1][warp] = (uint32_t)__popc(mb);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    uint32_t total = 0;
+#pragma unroll
+    for (int w = 0; w < kShadeBlock / 32; ++w) {
+      const uint32_t c = s_cnt[threadIdx.x][w];
+      s_cnt[threadIdx.x][w] = total;  // exclusive prefix
+      total += c;
+    }
+    uint32_t* ctr = threadIdx.x == 0 ? counter_a : counter_b;
+    s_base[threadIdx.x] = (total && ctr) ? atomicAdd(ctr, total) : 0u;
+  }
+  __syncthreads();
+  BlockAppend r;
+  r.slot_a = s_base[0] + s_cnt[0][warp] + (uint32_t)__popc(ma & ((1u << lane) - 1u));
+  r.slot_b = s_base[1] + s_cnt[1][warp] + (uint32_t)__popc(mb & ((1u << lane) - 1u));
+  __syncthreads();  // s_cnt / s_base are reused by the next round
+  return r;
+}
+
 // Orthonormal basis around unit n (Duff et al. 2017), operation order as in the spec.
 __device__ __forceinline__ void onb(f3 n, f3& t, f3& b) {
   const float sign = copysignf(1.0f, n.z);
@@ -71,12 +108,16 @@ __global__ void __launch_bounds__(kShadeBlock) raygen_kernel(const PassParams p)
       const f3 d = primary_dir(p.cam, p.im, x, y, jx, jy);
       p.st.ray_o[id] = make_float4(p.cam.origin.x, p.cam.origin.y, p.cam.origin.z, p.ip.tnear);
       p.st.ray_d[id] = make_float4(d.x, d.y, d.z, __int_as_float(0x7f800000));
-      p.st.thr[id] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(kFlagSpecular));  // bounce 0, camera = specular
-      p.st.L[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+      // throughput (1,1,1 | specular) and radiance 0 of a camera ray are implied at bounce 0: not stored
     }
-    const uint32_t slot = warp_append(p.st.counters + slot_queue_count(0), live);
-    if (live) p.st.queue[0][slot] = id;
+    if (p.im.part_world <= 1u) {
+      if (live) p.st.queue[0][id] = id;  // every pixel is owned: the queue is the identity, no atomics
+    } else {
+      const uint32_t slot = warp_append(p.st.counters + slot_queue_count(0), live);
+      if (live) p.st.queue[0][slot] = id;
+    }
   }
+  if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = total;
 }
 
 // ---- K3 ----------------------------------------------------------------------------------------------
@@ -109,15 +150,16 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const ShadeLaunch a)
       const uint32_t frame = p.first_frame + s * p.frame_stride;
       const uint2 h = st.hit[path];
       const float t = __uint_as_float(h.x);
-      const float4 o4 = st.ray_o[path], d4 = st.ray_d[path], thr4 = st.thr[path];
+      const float4 o4 = st.ray_o[path], d4 = st.ray_d[path];
+      const float4 thr4 = a.bounce == 0 ? make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(kFlagSpecular)) : st.thr[path];
       f3 o = mk3(o4.x, o4.y, o4.z);
       const f3 d = mk3(d4.x, d4.y, d4.z);
       f3 thr = mk3(thr4.x, thr4.y, thr4.z);
       const uint32_t flags = __float_as_uint(thr4.w);
       const bool specular_in = (flags & kFlagSpecular) != 0u;
-      float4 L4 = st.L[path];
+      const float4 L4 = a.bounce == 0 ? make_float4(0.f, 0.f, 0.f, 0.f) : st.L[path];
       f3 L = mk3(L4.x, L4.y, L4.z);
-      bool L_dirty = false;
+      bool L_dirty = a.bounce == 0;  // the first shade initialises the path's radiance slot
 
       if (a.bounce == 0 && s == 0 && p.aov_prim != nullptr) {
         p.aov_prim[pixel] = h.y == 0xFFFFFFFFu ? 0xFFFFFFFFu : __float_as_uint(__ldg(p.scene.tris + 3 * (size_t)h.y).w);
@@ -282,12 +324,9 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const ShadeLaunch a)
       }
       if (L_dirty) st.L[path] = make_float4(L.x, L.y, L.z, 0.f);
     }
-    const uint32_t slot = warp_append(next_count, cont);
-    if (cont) qout[slot] = path;
-    if (use_nee) {
-      const uint32_t sslot = warp_append(shadow_count, shadow);
-      if (shadow) st.shadow_queue[sslot] = path;
-    }
+    const BlockAppend ap = block_append2(next_count, cont, use_nee ? shadow_count : nullptr, shadow);
+    if (cont) qout[ap.slot_a] = path;
+    if (shadow) st.shadow_queue[ap.slot_b] = path;
   }
   const uint64_t ws = warp_sum_u32(n_shades), wp = warp_sum_u32(n_paths);
   if ((threadIdx.x & 31u) == 0u && (ws | wp)) {
