@@ -8,6 +8,8 @@
 // lanes busy until the queue drains.  Traversal stack: 8 entries per thread in shared memory (interleaved
 // by thread id: conflict-free 64-bit accesses), the rest in local memory.  Node and triangle fetches are
 // 128-bit read-only loads (5 per node, 3 per triangle).
+#include <cstdlib>
+
 #include "bvh8_traverse.cuh"
 #include "kernels.h"
 
@@ -16,7 +18,8 @@ namespace {
 
 constexpr int kSharedStack = 8;
 constexpr int kLocalStack = 32;
-constexpr int kRefillThreshold = 20;
+constexpr int kRefillThreshold = 26;
+constexpr int kPoolRays = 64;
 
 struct DeviceStack {
   uint2* shared_base;  // &smem[threadIdx.x], stride blockDim.x
@@ -43,7 +46,7 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
     trace_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
                  const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
                  uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
-                 const float4* __restrict__ contrib, unsigned long long* __restrict__ stats) {
+                 const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold) {
   __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
   const uint32_t n = *count_ptr;
   const unsigned lane = threadIdx.x & 31u;
@@ -52,6 +55,7 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
   stack.sp = 0;
 
   bool active = false, drained = false;
+  uint32_t pool_next = 0, pool_left = 0;  // warp-uniform
   uint32_t path = 0;
   RayPre r;
   float tnear = 0.f, tmax = 0.f, tmin_box = 0.f;
@@ -63,13 +67,23 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
     // ---- refill idle lanes (warp-synchronous) ----
     const unsigned idle = __ballot_sync(0xffffffffu, !active);
     if (idle && !drained) {
-      uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(work_counter, (uint32_t)__popc(idle));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (base >= n) drained = true;
+      // The warp owns a pool of kPoolRays consecutive queue entries, claimed with ONE atomic; idle lanes are
+      // served from the pool, so the number of global atomics is n / kPoolRays however often lanes refill.
+      const uint32_t want = (uint32_t)__popc(idle);
+      if (pool_left < want) {  // warp-uniform
+        // the few entries left in the old pool are served first, the new pool next time round
+        if (pool_left == 0u) {
+          uint32_t base = 0;
+          if (lane == 0) base = atomicAdd(work_counter, (uint32_t)kPoolRays);
+          pool_next = __shfl_sync(0xffffffffu, base, 0);
+          pool_left = pool_next < n ? min((uint32_t)kPoolRays, n - pool_next) : 0u;
+          if (pool_left == 0u) drained = true;
+        }
+      }
       if (!active) {
-        const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-        if (i < n) {
+        const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        const uint32_t i = pool_next + rank;
+        if (rank < pool_left) {
           path = queue[i];
           const float4 o4 = ray_o[path], d4 = ray_d[path];
           r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
@@ -89,6 +103,9 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
           active = true;
         }
       }
+      const uint32_t served = min(want, pool_left);
+      pool_next += served;
+      pool_left -= served;
     }
     if (__ballot_sync(0xffffffffu, active) == 0u) break;
 
@@ -134,7 +151,7 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
       }
       const unsigned act = __ballot_sync(0xffffffffu, active);
       if (act == 0u) break;
-      if (!drained && __popc(act) < kRefillThreshold) break;
+      if (!drained && __popc(act) < refill_threshold) break;
     }
   }
   if (kCount) {
@@ -147,6 +164,16 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
 }
 
+// Tuning knob (profiles/r01_notes.md): lanes are refilled when fewer than this many of a warp's 32 are busy.
+int refill_threshold() {
+  static const int v = [] {
+    const char* e = getenv("CUDAPT_REFILL_THRESHOLD");
+    const int x = e ? atoi(e) : kRefillThreshold;
+    return x < 1 ? 1 : (x > 32 ? 32 : x);
+  }();
+  return v;
+}
+
 }  // namespace
 
 cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count,
@@ -156,11 +183,11 @@ cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue
   if (counting)
     trace_kernel<false, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
                                                       st.counters + slot_queue_count(bounce),
-                                                      st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters);
+                                                      st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters, refill_threshold());
   else
     trace_kernel<false, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
                                                        st.counters + slot_queue_count(bounce),
-                                                       st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters);
+                                                       st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters, refill_threshold());
   return cudaGetLastError();
 }
 
@@ -170,11 +197,11 @@ cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool count
   if (counting)
     trace_kernel<true, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
                                                      st.counters + slot_shadow_count(bounce),
-                                                     st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters);
+                                                     st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters, refill_threshold());
   else
     trace_kernel<true, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
                                                       st.counters + slot_shadow_count(bounce),
-                                                      st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters);
+                                                      st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters, refill_threshold());
   return cudaGetLastError();
 }
 
