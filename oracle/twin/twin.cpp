@@ -279,19 +279,31 @@ struct Mesh {
   std::vector<uint32_t> lights;  // emissive triangle indices, ascending
 };
 
-// Moller-Trumbore on the stored (v0, e1, e2) record; two-sided; fixed operation order.
+// Moller-Trumbore on the stored (v0, e1, e2) record; two-sided; fixed operation order.  The inside test is
+// done on the det-scaled barycentrics (sign of det folded in by flipping sign bits, which is exact), so the
+// only division is t = (e2 . q) / det for candidates that are inside.  (DESIGN.md "Mesh integrator numerics")
+inline float flip_sign(float x, uint32_t sign_bit) {
+  uint32_t u;
+  std::memcpy(&u, &x, 4);
+  u ^= sign_bit;
+  std::memcpy(&x, &u, 4);
+  return x;
+}
 inline bool tri_hit(const Tri& T, V3 o, V3 d, float& t, float& bu, float& bv) {
   const V3 pv = cross(d, T.e2);
   const float det = dot(T.e1, pv);
   if (det == 0.0f) return false;
-  const float inv = 1.0f / det;
+  uint32_t sb;
+  std::memcpy(&sb, &det, 4);
+  sb &= 0x80000000u;
+  const float adet = flip_sign(det, sb);  // |det|
   const V3 tv = o - T.v0;
-  const float u = dot(tv, pv) * inv;
-  if (!(u >= 0.0f && u <= 1.0f)) return false;
+  const float u = flip_sign(dot(tv, pv), sb);
+  if (!(u >= 0.0f && u <= adet)) return false;
   const V3 qv = cross(tv, T.e1);
-  const float v = dot(d, qv) * inv;
-  if (!(v >= 0.0f && (u + v) <= 1.0f)) return false;
-  t = dot(T.e2, qv) * inv;
+  const float v = flip_sign(dot(d, qv), sb);
+  if (!(v >= 0.0f && (u + v) <= adet)) return false;
+  t = dot(T.e2, qv) / det;
   bu = u;
   bv = v;
   return true;

@@ -7,8 +7,10 @@
 //                                                     child slot s is an internal node)
 //   w1: u32 child_base (index of the first internal child; internal children are contiguous, in slot order)
 //       u32 tri_base   (index of the first triangle of this node's leaf children; contiguous)
-//       u8 meta[8]     (per slot: 0 = empty; internal: 0b001_11sss (sss = slot); leaf: unary triangle count
-//                       in the top 3 bits (001/011/111) | offset from tri_base in the low 5 bits)
+//       u32 tri_valid  (bit 3*s + j set <=> the leaf child in slot s owns a j-th triangle, j < 3; the node's
+//                       triangles are stored contiguously in (slot, j) order, so the triangle behind bit b is
+//                       tri_base + popc(tri_valid & ((1 << b) - 1)))
+//       u32 reserved
 //   w2: u8 qlo_x[8], qlo_y[8]      w3: u8 qlo_z[8], qhi_x[8]      w4: u8 qhi_y[8], qhi_z[8]
 // Child box = p + q * 2^(e-127), rounded outwards by the builder (exact-arithmetic conservative).
 //
@@ -31,7 +33,8 @@ struct Bvh8Node {
   uint8_t imask;
   uint32_t child_base;
   uint32_t tri_base;
-  uint8_t meta[8];
+  uint32_t tri_valid;
+  uint32_t reserved;
   uint8_t qlo_x[8], qlo_y[8], qlo_z[8];
   uint8_t qhi_x[8], qhi_y[8], qhi_z[8];
 };

@@ -73,26 +73,29 @@ __host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d) {
   return r;
 }
 
-// Moller-Trumbore, two-sided, fixed operation order (== oracle/twin tri_hit).
+// Moller-Trumbore, two-sided, fixed operation order (DESIGN.md "Mesh integrator numerics").  Inside test on
+// the det-scaled barycentrics with the sign of det folded in by an exact sign-bit flip; the one IEEE division
+// (t = (e2 . q) / det) is only reached by candidates that are inside, so the common reject paths cost ~25 and
+// ~45 instructions instead of ~90 (profiles/r01_notes.md: triangle tests ran at 4/32 lanes, 27 % of issue).
 __host__ __device__ __forceinline__ bool tri_test(f3 v0, f3 e1, f3 e2, f3 o, f3 d, float& t) {
   const f3 pv = cross3(d, e2);
   const float det = dot3(e1, pv);
   if (det == 0.0f) return false;
-  const float inv = 1.0f / det;
+  const uint32_t sb = pt_as_uint(det) & 0x80000000u;
+  const float adet = pt_as_float(pt_as_uint(det) ^ sb);
   const f3 tv = o - v0;
-  const float u = dot3(tv, pv) * inv;
-  if (!(u >= 0.0f && u <= 1.0f)) return false;
+  const float u = pt_as_float(pt_as_uint(dot3(tv, pv)) ^ sb);
+  if (!(u >= 0.0f && u <= adet)) return false;
   const f3 qv = cross3(tv, e1);
-  const float v = dot3(d, qv) * inv;
-  if (!(v >= 0.0f && (u + v) <= 1.0f)) return false;
-  t = dot3(e2, qv) * inv;
+  const float v = pt_as_float(pt_as_uint(dot3(d, qv)) ^ sb);
+  if (!(v >= 0.0f && (u + v) <= adet)) return false;
+  t = dot3(e2, qv) / det;
   return true;
 }
 
-// Tests the 8 quantised child boxes of one node; returns the hit mask: bits 24..31 = internal children by
-// traversal priority (slot ^ octinv), bits 0..23 = triangles (offset from tri_base).
-__host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, const uint4 w1, const uint4 w2, const uint4 w3,
-                                                            const uint4 w4, const RayPre& r, float tmin, float tmax) {
+// Tests the 8 quantised child boxes of one node; returns an 8-bit mask, bit s = the box in slot s is hit.
+__host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, const uint4 w2, const uint4 w3, const uint4 w4,
+                                                            const RayPre& r, float tmin, float tmax) {
   const float px = pt_as_float(w0.x), py = pt_as_float(w0.y), pz = pt_as_float(w0.z);
   const uint32_t ew = w0.w;
   const float adjx = pt_as_float((ew & 0xFFu) << 23) * r.idir.x;
@@ -104,49 +107,61 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
   // widened exit so rounding in the slab arithmetic can never cull a box the exact test would enter
   const float tmax_w = tmax * 1.000002f;
-  const uint32_t octinv4 = r.octinv * 0x01010101u;
-  uint32_t hitmask = 0;
+  uint32_t hits = 0;
 #pragma unroll
   for (int half = 0; half < 2; ++half) {
-    const uint32_t meta4 = half ? w1.w : w1.z;
-    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-    const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xFFu;
-    const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
-    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
     const uint32_t lox = half ? w2.y : w2.x, loy = half ? w2.w : w2.z, loz = half ? w3.y : w3.x;
     const uint32_t hix = half ? w3.w : w3.z, hiy = half ? w4.y : w4.x, hiz = half ? w4.w : w4.z;
     const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
     const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
-#define PT_CHILD(J)                                                                                      \
-    {                                                                                                    \
-      const float t0x = fmaf(byte_as_float<J>(nearx), adjx, orgx);                                       \
-      const float t0y = fmaf(byte_as_float<J>(neary), adjy, orgy);                                       \
-      const float t0z = fmaf(byte_as_float<J>(nearz), adjz, orgz);                                       \
-      const float t1x = fmaf(byte_as_float<J>(farx), adjx, orgx);                                        \
-      const float t1y = fmaf(byte_as_float<J>(fary), adjy, orgy);                                        \
-      const float t1z = fmaf(byte_as_float<J>(farz), adjz, orgz);                                        \
-      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                       \
-      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));                                     \
-      /* an empty slot has child_bits 0, which keeps it out of the mask whatever its box test says */    \
-      if (cmin <= cmax) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
+#define PT_CHILD(J)                                                                \
+    {                                                                              \
+      const float t0x = fmaf(byte_as_float<J>(nearx), adjx, orgx);                 \
+      const float t0y = fmaf(byte_as_float<J>(neary), adjy, orgy);                 \
+      const float t0z = fmaf(byte_as_float<J>(nearz), adjz, orgz);                 \
+      const float t1x = fmaf(byte_as_float<J>(farx), adjx, orgx);                  \
+      const float t1y = fmaf(byte_as_float<J>(fary), adjy, orgy);                  \
+      const float t1z = fmaf(byte_as_float<J>(farz), adjz, orgz);                  \
+      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                 \
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));               \
+      /* empty slots carry an inverted box (255 > 0) and can never pass */        \
+      if (cmin <= cmax) hits |= 1u << (4 * half + J);                              \
     }
     PT_CHILD(0) PT_CHILD(1) PT_CHILD(2) PT_CHILD(3)
 #undef PT_CHILD
   }
-  return hitmask;
+  return hits;
+}
+
+// Bit s of an 8-bit mask -> bit (s ^ k): three conditional swaps (neighbours, pairs, nibbles).
+__host__ __device__ __forceinline__ uint32_t xor_permute8(uint32_t x, uint32_t k) {
+  const uint32_t a = ((x & 0x55u) << 1) | ((x >> 1) & 0x55u);
+  x = (k & 1u) ? a : x;
+  const uint32_t b = ((x & 0x33u) << 2) | ((x >> 2) & 0x33u);
+  x = (k & 2u) ? b : x;
+  const uint32_t c = ((x & 0x0Fu) << 4) | ((x >> 4) & 0x0Fu);
+  return (k & 4u) ? c : x;
+}
+// Bit s of an 8-bit mask -> bits 3s..3s+2 of a 24-bit mask.
+__host__ __device__ __forceinline__ uint32_t spread8_to_24(uint32_t x) {
+  x = (x ^ (x << 8)) & 0x00F00Fu;
+  x = (x ^ (x << 4)) & 0x0C30C3u;
+  x = (x ^ (x << 2)) & 0x249249u;
+  return x * 7u;
 }
 
 // Stack concept: void push(uint2), uint2 pop(), bool empty().
 
 // One traversal step.  Precondition: ngroup has at least one internal child left (ngroup.y > 0x00FFFFFF).
 // Takes the highest-priority child, pushes what is left of the group, fetches that node (5 x LDG.128) and
-// tests its 8 children.  On return ngroup describes the fetched node's internal hits and (tri_base, tmask)
-// its triangle hits.
+// tests its 8 children.  On return ngroup describes the fetched node's internal hits (bits 24..31, by
+// traversal priority slot ^ octinv) and (tri_base, tri_valid, tmask) its triangle hits (tmask bit b = candidate
+// triangle tri_base + popc(tri_valid & ((1 << b) - 1))).
 template <class Stack>
 __host__ __device__ __forceinline__ void node_step(const uint4* __restrict__ nodes, const RayPre& r, float tmin_box,
                                                    float tmax, uint2& ngroup, Stack& stack, uint32_t& tri_base,
-                                                   uint32_t& tmask) {
+                                                   uint32_t& tri_valid, uint32_t& tmask) {
   const int bit = pt_bfind(ngroup.y);
   ngroup.y &= ~(1u << bit);
   const uint32_t base = ngroup.x, imask = ngroup.y & 0xFFu;
@@ -155,10 +170,12 @@ __host__ __device__ __forceinline__ void node_step(const uint4* __restrict__ nod
   const uint32_t rel = (uint32_t)pt_popc(imask & ~(0xFFFFFFFFu << slot));
   const uint4* np = nodes + 5 * (size_t)(base + rel);
   const uint4 w0 = PT_LDG4(np + 0), w1 = PT_LDG4(np + 1), w2 = PT_LDG4(np + 2), w3 = PT_LDG4(np + 3), w4 = PT_LDG4(np + 4);
-  const uint32_t hm = intersect_node(w0, w1, w2, w3, w4, r, tmin_box, tmax);
-  ngroup = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+  const uint32_t hits = intersect_node(w0, w2, w3, w4, r, tmin_box, tmax);
+  const uint32_t node_imask = w0.w >> 24;
+  ngroup = make_uint2(w1.x, (xor_permute8(hits & node_imask, r.octinv) << 24) | node_imask);
   tri_base = w1.y;
-  tmask = hm & 0x00FFFFFFu;
+  tri_valid = w1.z;
+  tmask = spread8_to_24(hits) & tri_valid;
 }
 
 // Tests triangle `tri`; returns true when an any-hit query is satisfied.  Closest-hit rule: smallest
@@ -201,14 +218,15 @@ __host__ __device__ __forceinline__ void bvh8_trace(const uint4* __restrict__ no
   const float tmin_box = tnear * 0.5f;
   uint2 ngroup = make_uint2(0u, 0x80000000u);  // the root, as "slot 7^octinv of a virtual parent"
   for (;;) {
-    uint32_t tri_base, tmask;
-    node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tmask);
+    uint32_t tri_base, tri_valid, tmask;
+    node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tri_valid, tmask);
     if (kCount) ++n_nodes;
     while (tmask) {
       const int ti = pt_bfind(tmask);
       tmask &= ~(1u << ti);
       if (kCount) ++n_tris;
-      if (tri_step<kAnyHit>(tris, tri_base + (uint32_t)ti, r, tnear, tmax, hit)) return;
+      const uint32_t tri = tri_base + (uint32_t)pt_popc(tri_valid & ((1u << ti) - 1u));
+      if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) return;
     }
     if (ngroup.y <= 0x00FFFFFFu) {
       if (stack.empty()) return;

@@ -325,13 +325,11 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
       if (i < 0) continue;
       if (!ch[i].leaf) {
         N.imask |= (uint8_t)(1u << s);
-        N.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
         queue.push_back({ch[i].node2, next_internal++, w.depth + 1});
       } else {
         const Node2& leaf = n2[ch[i].node2];
         const uint32_t cnt = leaf.count;  // 1..3
-        const uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
-        N.meta[s] = (uint8_t)((unary << 5) | tri_off);
+        N.tri_valid |= ((1u << cnt) - 1u) << (3 * s);
         for (uint32_t j = 0; j < cnt; ++j) {
           const uint32_t prim = B.perm[leaf.first + j];
           out->tri_of_prim[prim] = (uint32_t)out->tris.size();

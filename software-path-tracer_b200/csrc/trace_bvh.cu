@@ -114,15 +114,16 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
     // reconverges the warp, so node steps always execute with all active lanes together ----
     for (;;) {
       if (active) {
-        uint32_t tri_base, tmask;
-        node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tmask);
+        uint32_t tri_base, tri_valid, tmask;
+        node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tri_valid, tmask);
         if (kCount) ++n_nodes;
         bool finished = false;
         while (tmask) {
           const int ti = pt_bfind(tmask);
           tmask &= ~(1u << ti);
           if (kCount) ++n_tris;
-          if (tri_step<kAnyHit>(tris, tri_base + (uint32_t)ti, r, tnear, tmax, hit)) {
+          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & ((1u << ti) - 1u));
+          if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {
             finished = true;
             break;
           }
