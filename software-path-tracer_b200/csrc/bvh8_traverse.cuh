@@ -42,7 +42,11 @@ inline int pt_popc(uint32_t x) { return __builtin_popcount(x); }
 template <int J>
 __host__ __device__ __forceinline__ float byte_as_float(uint32_t word) {
 #ifdef __CUDA_ARCH__
-  return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + J)) - 8388608.0f;
+  // selector as the immediate, the 2^23 pattern in a register (one register for all 48 conversions); with
+  // __byte_perm() ptxas kept 0x4B000000 as the immediate and re-materialised a selector register per PRMT
+  uint32_t v;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(v) : "r"(word), "r"(0x4B000000u), "n"(0x7540 + J));
+  return __uint_as_float(v) - 8388608.0f;
 #else
   return (float)((word >> (8 * J)) & 0xFFu);
 #endif

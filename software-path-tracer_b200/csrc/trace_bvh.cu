@@ -41,8 +41,8 @@ struct DeviceStack {
 
 // One resumable traversal state per lane.  The generic bvh8_trace() in bvh8_traverse.cuh runs a ray to
 // completion; here the same steps are driven by an outer loop that can interleave refills.
-template <bool kAnyHit, bool kCount>
-__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM)
+template <bool kAnyHit, bool kCount, int kBlocksPerSM>
+__global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
     trace_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
                  const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
                  uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
@@ -175,35 +175,55 @@ int refill_threshold() {
   return v;
 }
 
+// Register budget knob: CTAs per SM the kernel is compiled for (8 -> 64 registers, 6 -> 80, 5 -> 96).
+int trace_blocks_per_sm() {
+  static const int v = [] {
+    const char* e = getenv("CUDAPT_TRACE_BLOCKS");
+    const int x = e ? atoi(e) : kTraceBlocksPerSM;
+    return (x == 5 || x == 6 || x == 7 || x == 8) ? x : kTraceBlocksPerSM;
+  }();
+  return v;
+}
+
+template <bool kAnyHit>
+cudaError_t launch_trace(const PassParams& p, const float4* ro, const float4* rd, const uint32_t* queue, uint32_t* count,
+                         uint32_t* work, uint2* hit, float4* L, const float4* contrib, bool counting, int sm_count,
+                         cudaStream_t s) {
+  const int bps = trace_blocks_per_sm();
+  const dim3 grid(sm_count * bps), block(kTraceBlock);
+  const int thr = refill_threshold();
+#define PT_LAUNCH(B, C)                                                                                                 \
+  trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L, contrib, \
+                                                     p.counters, thr)
+#define PT_PICK(B)          \
+  if (counting)             \
+    PT_LAUNCH(B, true);     \
+  else                      \
+    PT_LAUNCH(B, false)
+  switch (bps) {
+    case 5: PT_PICK(5); break;
+    case 6: PT_PICK(6); break;
+    case 7: PT_PICK(7); break;
+    default: PT_PICK(8); break;
+  }
+#undef PT_PICK
+#undef PT_LAUNCH
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count,
                                  cudaStream_t s) {
-  const dim3 grid(sm_count * kTraceBlocksPerSM), block(kTraceBlock);
   const WavefrontState& st = p.st;
-  if (counting)
-    trace_kernel<false, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
-                                                      st.counters + slot_queue_count(bounce),
-                                                      st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters, refill_threshold());
-  else
-    trace_kernel<false, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.ray_o, st.ray_d, st.queue[queue_in],
-                                                       st.counters + slot_queue_count(bounce),
-                                                       st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, p.counters, refill_threshold());
-  return cudaGetLastError();
+  return launch_trace<false>(p, st.ray_o, st.ray_d, st.queue[queue_in], st.counters + slot_queue_count(bounce),
+                             st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, counting, sm_count, s);
 }
 
 cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool counting, int sm_count, cudaStream_t s) {
-  const dim3 grid(sm_count * kTraceBlocksPerSM), block(kTraceBlock);
   const WavefrontState& st = p.st;
-  if (counting)
-    trace_kernel<true, true><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
-                                                     st.counters + slot_shadow_count(bounce),
-                                                     st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters, refill_threshold());
-  else
-    trace_kernel<true, false><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, st.sh_o, st.sh_d, st.shadow_queue,
-                                                      st.counters + slot_shadow_count(bounce),
-                                                      st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, p.counters, refill_threshold());
-  return cudaGetLastError();
+  return launch_trace<true>(p, st.sh_o, st.sh_d, st.shadow_queue, st.counters + slot_shadow_count(bounce),
+                            st.counters + slot_shadow_work(bounce), nullptr, st.L, st.sh_c, counting, sm_count, s);
 }
 
 }  // namespace cudapt
