@@ -82,7 +82,7 @@ struct PassParams {
 };
 
 constexpr int kTraceBlock = 128;
-constexpr int kTraceBlocksPerSM = 8;
+constexpr int kTraceBlocksPerSM = 9;
 constexpr int kShadeBlock = 256;
 
 cudaError_t launch_raygen(const PassParams& p, int sm_count, cudaStream_t s);

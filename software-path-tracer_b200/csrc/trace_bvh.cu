@@ -180,7 +180,7 @@ int trace_blocks_per_sm() {
   static const int v = [] {
     const char* e = getenv("CUDAPT_TRACE_BLOCKS");
     const int x = e ? atoi(e) : kTraceBlocksPerSM;
-    return (x == 5 || x == 6 || x == 7 || x == 8) ? x : kTraceBlocksPerSM;
+    return (x >= 5 && x <= 12) ? x : kTraceBlocksPerSM;
   }();
   return v;
 }
@@ -204,6 +204,9 @@ cudaError_t launch_trace(const PassParams& p, const float4* ro, const float4* rd
     case 5: PT_PICK(5); break;
     case 6: PT_PICK(6); break;
     case 7: PT_PICK(7); break;
+    case 9: PT_PICK(9); break;
+    case 10: PT_PICK(10); break;
+    case 12: PT_PICK(12); break;
     default: PT_PICK(8); break;
   }
 #undef PT_PICK
