@@ -10,7 +10,7 @@ CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace
 HDR      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cudapt.h
 OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o
 
-all: $(PKG)/libcudapt.so oracle
+all: $(PKG)/libcudapt.so oracle host
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDR)
 	$(NVCC) $(NVFLAGS) -dc -o $@ $< 2> $@.ptxas.log || (cat $@.ptxas.log; false)
@@ -24,7 +24,20 @@ $(PKG)/libcudapt.so: $(OBJ)
 oracle:
 	$(MAKE) -C oracle all
 
+# C++ host side: render::PathTracer adapter (product, compiled against the reference's public headers) and the
+# headless two-backend driver (test scaffolding; links the Tier-1 oracle for the reference's own TUs).  Needs the
+# reference tree, so it is only (re)built where /root/reference is mounted; the binary travels to the GPU box.
+REF      ?= /root/reference
+REFINC   := -I$(REF)/libs/render/include -I$(REF)/libs/render/src -I$(REF)/libs/render/vendor/glm
+host: $(PKG)/libcudapt.so oracle
+	@if [ -d $(REF)/libs/render/src ]; then $(MAKE) build/headless_compare; else echo "host: $(REF) absent, keeping prebuilt build/"; fi
+
+build/headless_compare: $(PKG)/host/CUDAPathTracer.cpp $(PKG)/host/CUDAPathTracer.h tests/cpp/headless_compare.cpp include/cudapt.h
+	mkdir -p build
+	$(CXX) -std=gnu++23 -O2 -w $(REFINC) -Iinclude -I$(PKG)/host -o $@ $(PKG)/host/CUDAPathTracer.cpp tests/cpp/headless_compare.cpp \
+	    -L$(PKG) -lcudapt -Loracle/_ref -lref_render -Wl,-rpath,'$$ORIGIN/../$(PKG):$$ORIGIN/../oracle/_ref'
+
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.ptxas.log $(PKG)/libcudapt.so
 	$(MAKE) -C oracle clean
-.PHONY: all oracle clean
+.PHONY: all oracle host clean

@@ -213,6 +213,7 @@ def main():
     import torch
     import torch.distributed as dist
     pt = importlib.import_module("software-path-tracer_b200")
+    part = importlib.import_module("software-path-tracer_b200.partition")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
@@ -233,7 +234,7 @@ def main():
         tr.upload_mesh(scene["v"], scene["t"], scene["m"], scene["mats"])
         scene_bytes = int(tr.stats().accel_bytes)
     if world > 1:
-        tr.set_frame_range(rank + 1, world)  # sample-range sharding
+        tr.set_frame_range(*part.frame_range(rank, world))  # sample-range sharding
 
     stream = torch.cuda.ExternalStream(tr.stream_handle, device=local_rank)
     n_px = W * H
@@ -251,7 +252,7 @@ def main():
         tr.render(spp)
         if world > 1:
             with torch.cuda.stream(stream):
-                dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+                part.reduce_accum(accum_t, dst=0)
 
     def sync_all():
         tr.synchronize()
@@ -309,7 +310,7 @@ def main():
         tr.render(spp)
         if world > 1:
             with torch.cuda.stream(stream):
-                dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+                part.reduce_accum(accum_t, dst=0)
             tr.set_frame_count(spp * world if rank == 0 else spp)
         tr.resolve_rgba8(host_rgba)                  # resolve kernel + D2H + sync
 

@@ -1,0 +1,56 @@
+// render::PathTracer backend that forwards to the C ABI of libcudapt.so (include/cudapt.h).
+//
+// Drop-in sibling of the reference's CPUPathTracer
+// (libs/render/src/engines/pathtracer/backends/cpu/CPUPathTracer.h:21-75): same eight overrides, same
+// invalidation rules (CPUPathTracer.cpp:119-161), same fail-fast error convention (render::verify).  It is
+// compiled inside the reference tree (it includes the reference's own public headers); see INTEGRATION.md for
+// the two-line factory change that registers it.
+#pragma once
+
+#include <memory>
+#include <string>
+
+#include "render/PathTracer.h"
+
+struct cudapt_ctx;
+
+namespace render
+{
+	class CUDAPathTracer : public PathTracer
+	{
+	public:
+		CUDAPathTracer();
+		~CUDAPathTracer() override;
+
+		void render() override;
+
+		void set_scene(std::shared_ptr<Scene> scene) override { m_scene = scene; }
+		void set_settings(std::shared_ptr<RenderSettings> settings) override { m_renderSettings = settings; }
+
+		std::shared_ptr<Scene> get_scene() const override { return m_scene; }
+		std::shared_ptr<RenderSettings> get_settings() const override { return m_renderSettings; }
+
+		std::string get_backend_name() const override { return "CUDA Path Tracer (sm_100a)"; }
+		// PathTracer::BackendType has no CUDA enumerator upstream (PathTracer.h:16-21); INTEGRATION.md appends
+		// GPU_CUDA = 3.  Until that lands the value is reported by ordinal.
+		BackendType get_backend_type() const override { return static_cast<BackendType>(3); }
+
+		const PathTracer::RenderResult &get_render_result() override;
+
+		// Extensions (not part of render::PathTracer): float accumulation read-back and counters.
+		cudapt_ctx *native_handle() const { return m_ctx; }
+
+	private:
+		void invalidate();
+		void upload_scene();
+
+		cudapt_ctx *m_ctx = nullptr;
+		std::shared_ptr<Scene> m_scene;
+		std::shared_ptr<RenderSettings> m_renderSettings;
+		PathTracer::RenderResult m_render_result;
+		uint32_t m_frameCount = 0;
+	};
+
+	// What the factory case added in INTEGRATION.md calls.
+	std::unique_ptr<PathTracer> create_cuda_path_tracer();
+}

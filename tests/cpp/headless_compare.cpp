@@ -1,0 +1,91 @@
+// Headless stand-in for the reference's App (src/App.cpp needs an SDL window: unavailable on this box).
+// Builds the scene of App.cpp:101-122 through the reference's own Scene API and drives TWO backends through the
+// unchanged render::PathTracer interface with the five calls App makes (create :98, set_settings :129,
+// set_scene :130, render() :231, get_render_result() :232): the reference's CPUPathTracer (against the Embree
+// stand-in) and CUDAPathTracer.  Compares the RGBA8 images they return.  Test scaffolding (links oracle/_ref).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <memory>
+
+#include "CUDAPathTracer.h"
+#include "render/Log.h"
+#include "render/PathTracer.h"
+#include "render/Scene.h"
+#include "render/Types.h"
+
+static std::shared_ptr<render::Scene> make_app_scene()
+{
+	auto scene = std::make_shared<render::Scene>();
+	{
+		auto s = scene->CreateNode<render::SphereObject>("123");
+		s->SetRadius(1.0f);
+		s->SetPosition(glm::vec3(0.0f, -1.0f, 5.0f));
+	}
+	{
+		auto s = scene->CreateNode<render::SphereObject>("123");
+		s->SetRadius(100.0f);
+		s->SetPosition(glm::vec3(0.0f, -102.0f, 5.0f));
+	}
+	const int dims = 5;
+	for (int x = -dims; x <= dims; x += 2)
+		for (int y = -dims; y <= dims; y += 2)
+		{
+			auto s = scene->CreateNode<render::SphereObject>("sphere");
+			s->SetRadius(0.5f);
+			s->SetPosition(glm::vec3((float)x, (float)y, 10.0f));
+		}
+	return scene;
+}
+
+static double drive(render::PathTracer &pt, uint32_t w, uint32_t h, int frames, std::vector<uint32_t> &out)
+{
+	auto settings = std::make_shared<render::RenderSettings>();
+	settings->setResolution(w, h);
+	settings->setSamplesPerPixel(64);
+	settings->setMaxBounces(8);
+	pt.set_settings(settings);
+	pt.set_scene(make_app_scene());
+	const auto t0 = std::chrono::steady_clock::now();
+	for (int f = 0; f < frames; ++f)
+	{
+		pt.render();
+		const auto &res = pt.get_render_result();
+		if (f == frames - 1)
+			out = res.image_buffer;
+	}
+	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+int main(int argc, char **argv)
+{
+	const uint32_t w = argc > 1 ? (uint32_t)std::atoi(argv[1]) : 640;
+	const uint32_t h = argc > 2 ? (uint32_t)std::atoi(argv[2]) : 360;
+	const int frames = argc > 3 ? std::atoi(argv[3]) : 16;
+	render::Log::set_callback([](render::LogLevel, std::string_view) {});
+	std::streambuf *old = std::cout.rdbuf(nullptr);  // the reference prints per node (Scene.h:171, CPUPathTracer.cpp:365-396)
+	std::vector<uint32_t> cpu_img, gpu_img;
+	auto cpu = render::PathTracer::create_path_tracer(render::PathTracer::BackendType::CPU_EMBREE);
+	const double cpu_s = drive(*cpu, w, h, frames, cpu_img);
+	auto gpu = render::create_cuda_path_tracer();
+	const double gpu_s = drive(*gpu, w, h, frames, gpu_img);
+	// resize + restart through the interface: change the resolution, render again
+	std::vector<uint32_t> cpu2, gpu2;
+	drive(*cpu, w / 2, h / 2, 2, cpu2);
+	drive(*gpu, w / 2, h / 2, 2, gpu2);
+	std::cout.rdbuf(old);
+	std::cout.clear();
+	size_t same = 0, same2 = 0;
+	for (size_t i = 0; i < cpu_img.size(); ++i) same += cpu_img[i] == gpu_img[i];
+	for (size_t i = 0; i < cpu2.size(); ++i) same2 += cpu2[i] == gpu2[i];
+	std::printf("backend cpu: %s | gpu: %s\n", cpu->get_backend_name().c_str(), gpu->get_backend_name().c_str());
+	std::printf("%ux%u x %d frames: identical RGBA8 pixels %zu/%zu; after resize %zu/%zu\n", w, h, frames, same, cpu_img.size(), same2,
+	            cpu2.size());
+	std::printf("wall: cpu %.3f s (%.2f Msamples/s), gpu %.4f s (%.1f Msamples/s) incl. per-frame get_render_result()\n", cpu_s,
+	            (double)w * h * frames / cpu_s / 1e6, gpu_s, (double)w * h * frames / gpu_s / 1e6);
+	const bool ok = cpu_img.size() == (size_t)w * h && same >= cpu_img.size() - cpu_img.size() / 10000 &&
+	                same2 >= cpu2.size() - cpu2.size() / 10000 - 1;
+	std::printf(ok ? "OK\n" : "MISMATCH\n");
+	return ok ? 0 : 1;
+}
