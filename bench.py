@@ -384,10 +384,30 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
         return {"bound": "hbm", "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None, "traffic": None,
                 "peak_source": peak_src, "note": "node/triangle counters unavailable"}
     bytes_per_path = R * (Nn * 80.0 + Nt * 48.0) + B * 160.0 + 32.0
-    alg_bytes = bytes_per_path * n_px * spp
-    achieved = alg_bytes / (render_ms * 1e-3) / 1e9
-    return {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-            "traffic": None, "peak_source": peak_src, "bytes_per_path": bytes_per_path, "R": R, "Nn": Nn, "Nt": Nt, "B": B}
+    # Dominant kernel = trace_kernel (closest-hit BVH traversal).  Its launches of the last render are timed
+    # inside libcudapt with CUDA-event pairs on the launch stream (stats.last_trace_ms = their sum).
+    # Algorithmic bytes of those launches: per ray 36 B in (ray + queue id) + 8 B out (hit) + Nn nodes x 80 B
+    # + Nt triangles x 48 B.  Reported per launch: both divided by the number of trace launches.
+    rays = float(st.rays)
+    trace_ms = float(st.last_trace_ms)
+    n_launches = max(1, -(-spp // int(wl["cfg"].get("samples_per_pass", 1))) * int(wl["cfg"].get("max_bounces", 4)))
+    trace_bytes = rays * (44.0 + Nn * 80.0 + Nt * 48.0)
+    achieved = trace_bytes / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "trace_dram_traffic.json")
+    if os.path.exists(tpath):
+        t = json.load(open(tpath)).get(wl["name"])
+        if t:
+            traffic = t["dram_bytes_per_ray"] * rays / n_launches
+    return {"bound": "hbm", "kernel": "trace_kernel<closest>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+            "frac": achieved / hbm_peak if achieved else None, "traffic": traffic,
+            "algorithmic_bytes_per_launch": trace_bytes / n_launches, "launch_ms": trace_ms / n_launches,
+            "launches_per_step": n_launches, "kernel_share_of_step": trace_ms / render_ms if render_ms else None,
+            "peak_source": peak_src, "bytes_per_ray": 44.0 + Nn * 80.0 + Nt * 48.0, "bytes_per_path_whole_step": bytes_per_path,
+            "whole_step_GBps": bytes_per_path * n_px * spp / (render_ms * 1e-3) / 1e9,
+            "R": R, "Nn": Nn, "Nt": Nt, "B": B,
+            "note": "BVH of c2/c3 is L2-resident, so DRAM traffic is far below the algorithmic bytes and the kernel is "
+                    "issue/latency bound (profiles/r01_notes.md); c4 (1.3 GB BVH) is the HBM-gather case"}
 
 
 if __name__ == "__main__":

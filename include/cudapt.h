@@ -96,6 +96,8 @@ typedef struct cudapt_stats {
   uint32_t n_triangles;
   uint32_t n_nodes;
   uint32_t n_spheres;
+  double last_trace_ms;      /* CUDA-event time of the closest-hit BVH traversal launches inside the most
+                                recent cudapt_render() (mesh integrator; 0 for the sphere megakernel) */
 } cudapt_stats;
 
 /* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */

@@ -50,6 +50,7 @@ class Stats(ctypes.Structure):
         ("kernel_launches", ctypes.c_uint64), ("render_ms", ctypes.c_double), ("last_render_ms", ctypes.c_double),
         ("accel_build_ms", ctypes.c_double), ("accel_bytes", ctypes.c_uint64), ("frame_count", ctypes.c_uint32),
         ("n_triangles", ctypes.c_uint32), ("n_nodes", ctypes.c_uint32), ("n_spheres", ctypes.c_uint32),
+        ("last_trace_ms", ctypes.c_double),
     ]
 
 

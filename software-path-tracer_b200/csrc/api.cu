@@ -48,7 +48,7 @@ struct cudapt_ctx {
 
   // stats
   uint64_t launches = 0;
-  double render_ms = 0.0, last_render_ms = 0.0;
+  double render_ms = 0.0, last_render_ms = 0.0, last_trace_ms = 0.0;
   bool timing_pending = false;
 };
 
@@ -133,6 +133,7 @@ int finish_timing(cudapt_ctx* ctx) {
   float ms = 0.f;
   CU_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->last_render_ms = ms;
+  ctx->last_trace_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_trace_ms() : 0.0;
   ctx->render_ms += ms;
   ctx->timing_pending = false;
   return CUDAPT_OK;
@@ -479,6 +480,7 @@ int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out) {
   out->kernel_launches = ctx->launches;
   out->render_ms = ctx->render_ms;
   out->last_render_ms = ctx->last_render_ms;
+  out->last_trace_ms = ctx->last_trace_ms;
   out->accel_build_ms = ctx->mesh.build_ms;
   out->accel_bytes = ctx->mesh.accel_bytes;
   out->frame_count = ctx->frame_count;

@@ -59,6 +59,9 @@ void MeshScene::invalidate_image_state() {
 }
 
 void MeshScene::release() {
+  for (cudaEvent_t e : trace_events_) cudaEventDestroy(e);
+  trace_events_.clear();
+  trace_events_used_ = 0;
   if (dev_) {
     dev_->free_state();
     dev_->free_scene();
@@ -135,6 +138,28 @@ bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
   return true;
 }
 
+void MeshScene::next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1) {
+  *e0 = *e1 = nullptr;
+  if (trace_events_used_ + 2 > 8192) return;  // very long renders: the tail is simply not timed per kernel
+  while (trace_events_.size() < trace_events_used_ + 2) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    trace_events_.push_back(e);
+  }
+  *e0 = trace_events_[trace_events_used_++];
+  *e1 = trace_events_[trace_events_used_++];
+}
+
+// Sum of the closest-hit traversal launches of the last render(); call after the stream has been synchronised.
+double MeshScene::collect_trace_ms() {
+  double total = 0.0;
+  for (size_t i = 0; i + 1 < trace_events_used_; i += 2) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, trace_events_[i], trace_events_[i + 1]) == cudaSuccess) total += ms;
+  }
+  return total;
+}
+
 static cudaError_t ensure_state(MeshDevice* d, uint32_t paths, uint32_t bounces) {
   if (d->state_paths >= paths && d->state_bounces >= bounces) return cudaSuccess;
   d->free_state();
@@ -162,6 +187,7 @@ static cudaError_t ensure_state(MeshDevice* d, uint32_t paths, uint32_t bounces)
 
 cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err) {
   *launches = 0;
+  trace_events_used_ = 0;
   if (!dev_ || !dev_->d_nodes) {
     *err = "accel not built";
     return cudaErrorInvalidValue;
@@ -207,7 +233,11 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     ++*launches;
     for (uint32_t b = 0; b < max_b; ++b) {
       const int qin = (int)(b & 1u);
+      cudaEvent_t e0 = nullptr, e1 = nullptr;
+      next_trace_events(&e0, &e1);  // per-launch timing of the dominant kernel (bench.py roofline)
+      if (e0) cudaEventRecord(e0, stream);
       R_TRY(launch_trace_closest(p, b, qin, a.counting, sm_count, stream), "trace_closest");
+      if (e1) cudaEventRecord(e1, stream);
       R_TRY(launch_shade(p, b, qin, sm_count, stream), "shade");
       *launches += 2;
       if (nee) {

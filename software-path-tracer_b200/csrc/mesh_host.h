@@ -42,6 +42,8 @@ class MeshScene {
   void release();
   uint32_t n_triangles() const { return n_tris_built_; }
   uint32_t n_nodes() const { return n_nodes_built_; }
+  // CUDA-event time of the closest-hit traversal launches of the last render() (call after a stream sync).
+  double collect_trace_ms();
 
  private:
   std::vector<float> vertices_;
@@ -50,6 +52,9 @@ class MeshScene {
   std::vector<cudapt_material> materials_;
   uint32_t n_tris_built_ = 0, n_nodes_built_ = 0;
   MeshDevice* dev_ = nullptr;
+  void next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1);
+  std::vector<cudaEvent_t> trace_events_;
+  size_t trace_events_used_ = 0;
 };
 
 }  // namespace cudapt
