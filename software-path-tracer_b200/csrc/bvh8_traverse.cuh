@@ -36,19 +36,21 @@ inline int pt_bfind(uint32_t x) { return 31 - __builtin_clz(x); }
 inline int pt_popc(uint32_t x) { return __builtin_popcount(x); }
 #endif
 
-// Byte j of `word` as a float.  On the device: PRMT splices the byte into the mantissa of 2^23 (0x4B000000)
-// and one FADD removes the bias -- two full-rate instructions instead of a shift/mask plus a quarter-rate I2F
-// (48 conversions per node made I2F the busiest pipe of the traversal kernel; profiles/r01_trace_notes.md).
+// 2^23 + (byte J of `word`) as a float: PRMT splices the byte into the mantissa of 2^23 (bit pattern `magic` =
+// 0x4B000000).  ONE full-rate instruction per conversion; the 2^23 bias is folded into the slab constants of
+// intersect_node().  (History, profiles/r01_notes.md: shift/mask + quarter-rate I2F -> PRMT + FADD -> PRMT.)
+// `magic` is carried in a register (RayPre::magic, from a kernel argument) so that ptxas keeps the SELECTOR
+// as the PRMT immediate; with a literal it kept 0x4B000000 as the immediate and re-materialised a selector
+// register for every PRMT.
 template <int J>
-__host__ __device__ __forceinline__ float byte_as_float(uint32_t word) {
+__host__ __device__ __forceinline__ float byte_as_biased_float(uint32_t word, uint32_t magic) {
 #ifdef __CUDA_ARCH__
-  // selector as the immediate, the 2^23 pattern in a register (one register for all 48 conversions); with
-  // __byte_perm() ptxas kept 0x4B000000 as the immediate and re-materialised a selector register per PRMT
   uint32_t v;
-  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(v) : "r"(word), "r"(0x4B000000u), "n"(0x7540 + J));
-  return __uint_as_float(v) - 8388608.0f;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(v) : "r"(word), "r"(magic), "n"(0x7540 + J));
+  return __uint_as_float(v);
 #else
-  return (float)((word >> (8 * J)) & 0xFFu);
+  (void)magic;
+  return 8388608.0f + (float)((word >> (8 * J)) & 0xFFu);
 #endif
 }
 
@@ -61,10 +63,12 @@ struct TraceHit {
 struct RayPre {
   f3 o, d, idir;
   uint32_t octinv;  // 7 ^ (direction sign octant)
+  uint32_t magic;   // 0x4B000000, see byte_as_biased_float()
 };
 
-__host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d) {
+__host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d, uint32_t magic = 0x4B000000u) {
   RayPre r;
+  r.magic = magic;
   r.o = o;
   r.d = d;
   const float kTiny = 1e-20f;
@@ -105,12 +109,21 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   const float adjx = pt_as_float((ew & 0xFFu) << 23) * r.idir.x;
   const float adjy = pt_as_float(((ew >> 8) & 0xFFu) << 23) * r.idir.y;
   const float adjz = pt_as_float(((ew >> 16) & 0xFFu) << 23) * r.idir.z;
-  const float orgx = (px - r.o.x) * r.idir.x;
-  const float orgy = (py - r.o.y) * r.idir.y;
-  const float orgz = (pz - r.o.z) * r.idir.z;
+  // t = q * adj + (p - o) * idir with q = (2^23 + q) - 2^23: the bias goes into the additive constant, and the
+  // rounding error that constant then carries (<= |org2| * 2^-24, i.e. about one quantisation step) is given
+  // back as slack, entry side down, exit side up, so the test stays conservative.
+  const float kBias = 8388608.0f;
+  const float org2x = fmaf(-kBias, adjx, (px - r.o.x) * r.idir.x);
+  const float org2y = fmaf(-kBias, adjy, (py - r.o.y) * r.idir.y);
+  const float org2z = fmaf(-kBias, adjz, (pz - r.o.z) * r.idir.z);
+  const float slx = fabsf(org2x) * 2.4e-7f, sly = fabsf(org2y) * 2.4e-7f, slz = fabsf(org2z) * 2.4e-7f;
+  const float o0x = org2x - slx, o1x = org2x + slx;
+  const float o0y = org2y - sly, o1y = org2y + sly;
+  const float o0z = org2z - slz, o1z = org2z + slz;
   const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
   // widened exit so rounding in the slab arithmetic can never cull a box the exact test would enter
   const float tmax_w = tmax * 1.000002f;
+  const uint32_t magic = r.magic;
   uint32_t hits = 0;
 #pragma unroll
   for (int half = 0; half < 2; ++half) {
@@ -121,15 +134,15 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
 #define PT_CHILD(J)                                                                \
     {                                                                              \
-      const float t0x = fmaf(byte_as_float<J>(nearx), adjx, orgx);                 \
-      const float t0y = fmaf(byte_as_float<J>(neary), adjy, orgy);                 \
-      const float t0z = fmaf(byte_as_float<J>(nearz), adjz, orgz);                 \
-      const float t1x = fmaf(byte_as_float<J>(farx), adjx, orgx);                  \
-      const float t1y = fmaf(byte_as_float<J>(fary), adjy, orgy);                  \
-      const float t1z = fmaf(byte_as_float<J>(farz), adjz, orgz);                  \
+      const float t0x = fmaf(byte_as_biased_float<J>(nearx, magic), adjx, o0x);    \
+      const float t0y = fmaf(byte_as_biased_float<J>(neary, magic), adjy, o0y);    \
+      const float t0z = fmaf(byte_as_biased_float<J>(nearz, magic), adjz, o0z);    \
+      const float t1x = fmaf(byte_as_biased_float<J>(farx, magic), adjx, o1x);     \
+      const float t1y = fmaf(byte_as_biased_float<J>(fary, magic), adjy, o1y);     \
+      const float t1z = fmaf(byte_as_biased_float<J>(farz, magic), adjz, o1z);     \
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                 \
       const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));               \
-      /* empty slots carry an inverted box (255 > 0) and can never pass */        \
+      /* empty slots (inverted boxes) may pass; imask / tri_valid keep them out */ \
       if (cmin <= cmax) hits |= 1u << (4 * half + J);                              \
     }
     PT_CHILD(0) PT_CHILD(1) PT_CHILD(2) PT_CHILD(3)

@@ -84,6 +84,7 @@ struct PassParams {
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = 9;
 constexpr int kShadeBlock = 256;
+constexpr int kShadeBlocksPerSM = 4;
 
 cudaError_t launch_raygen(const PassParams& p, int sm_count, cudaStream_t s);
 cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count, cudaStream_t s);

@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
     trace_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
                  const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
                  uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
-                 const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold) {
+                 const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold, const uint32_t magic) {
   __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
   const uint32_t n = *count_ptr;
   const unsigned lane = threadIdx.x & 31u;
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
         if (rank < pool_left) {
           path = queue[i];
           const float4 o4 = ray_o[path], d4 = ray_d[path];
-          r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+          r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), magic);
           if (kAnyHit) {
             tnear = d4.w;  // shadow rays: {o, tmax}, {d, tnear}
             tmax = o4.w;
@@ -194,7 +194,7 @@ cudaError_t launch_trace(const PassParams& p, const float4* ro, const float4* rd
   const int thr = refill_threshold();
 #define PT_LAUNCH(B, C)                                                                                                 \
   trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L, contrib, \
-                                                     p.counters, thr)
+                                                     p.counters, thr, 0x4B000000u)
 #define PT_PICK(B)          \
   if (counting)             \
     PT_LAUNCH(B, true);     \

@@ -127,7 +127,9 @@ struct ShadeLaunch {
   int queue_in;
 };
 
-__global__ void __launch_bounds__(kShadeBlock) shade_kernel(const ShadeLaunch a) {
+// 4 CTAs/SM (64 registers): the kernel is bound by the latency of its dependent gathers (queue -> hit ->
+// triangle -> material), so resident warps matter more than registers (profiles/r01_notes.md).
+__global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(const ShadeLaunch a) {
   const PassParams& p = a.p;
   const WavefrontState& st = p.st;
   const uint32_t n = st.counters[slot_queue_count(a.bounce)];
@@ -368,7 +370,7 @@ cudaError_t launch_raygen(const PassParams& p, int sm_count, cudaStream_t s) {
 
 cudaError_t launch_shade(const PassParams& p, uint32_t bounce, int queue_in, int sm_count, cudaStream_t s) {
   ShadeLaunch a{p, bounce, queue_in};
-  shade_kernel<<<sm_count * (2048 / kShadeBlock), kShadeBlock, 0, s>>>(a);
+  shade_kernel<<<sm_count * kShadeBlocksPerSM, kShadeBlock, 0, s>>>(a);
   return cudaGetLastError();
 }
 
