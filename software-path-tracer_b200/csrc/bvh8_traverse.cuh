@@ -113,13 +113,20 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   // rounding error that constant then carries (<= |org2| * 2^-24, i.e. about one quantisation step) is given
   // back as slack, entry side down, exit side up, so the test stays conservative.
   const float kBias = 8388608.0f;
-  const float org2x = fmaf(-kBias, adjx, (px - r.o.x) * r.idir.x);
-  const float org2y = fmaf(-kBias, adjy, (py - r.o.y) * r.idir.y);
-  const float org2z = fmaf(-kBias, adjz, (pz - r.o.z) * r.idir.z);
-  const float slx = fabsf(org2x) * 2.4e-7f, sly = fabsf(org2y) * 2.4e-7f, slz = fabsf(org2z) * 2.4e-7f;
+  const float orgx = (px - r.o.x) * r.idir.x, orgy = (py - r.o.y) * r.idir.y, orgz = (pz - r.o.z) * r.idir.z;
+#ifdef __CUDA_ARCH__
+  // directed rounding: the entry constant is rounded down, the exit constant up (FFMA.RM / FFMA.RP, full
+  // rate), so the boxes grow by at most one ulp of 2^23 * adj = one quantisation step in total
+  const float o0x = __fmaf_rd(-kBias, adjx, orgx), o1x = __fmaf_ru(-kBias, adjx, orgx);
+  const float o0y = __fmaf_rd(-kBias, adjy, orgy), o1y = __fmaf_ru(-kBias, adjy, orgy);
+  const float o0z = __fmaf_rd(-kBias, adjz, orgz), o1z = __fmaf_ru(-kBias, adjz, orgz);
+#else
+  const float org2x = fmaf(-kBias, adjx, orgx), org2y = fmaf(-kBias, adjy, orgy), org2z = fmaf(-kBias, adjz, orgz);
+  const float slx = fabsf(org2x) * 1.3e-7f, sly = fabsf(org2y) * 1.3e-7f, slz = fabsf(org2z) * 1.3e-7f;
   const float o0x = org2x - slx, o1x = org2x + slx;
   const float o0y = org2y - sly, o1y = org2y + sly;
   const float o0z = org2z - slz, o1z = org2z + slz;
+#endif
   const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
   // widened exit so rounding in the slab arithmetic can never cull a box the exact test would enter
   const float tmax_w = tmax * 1.000002f;

@@ -82,7 +82,7 @@ struct PassParams {
 };
 
 constexpr int kTraceBlock = 128;
-constexpr int kTraceBlocksPerSM = 9;
+constexpr int kTraceBlocksPerSM = 8;
 constexpr int kShadeBlock = 256;
 constexpr int kShadeBlocksPerSM = 4;
 
