@@ -7,9 +7,10 @@
 //                                                     child slot s is an internal node)
 //   w1: u32 child_base (index of the first internal child; internal children are contiguous, in slot order)
 //       u32 tri_base   (index of the first triangle of this node's leaf children; contiguous)
-//       u32 tri_valid  (bit 3*s + j set <=> the leaf child in slot s owns a j-th triangle, j < 3; the node's
-//                       triangles are stored contiguously in (slot, j) order, so the triangle behind bit b is
-//                       tri_base + popc(tri_valid & ((1 << b) - 1)))
+//       u32 tri_valid  (bit 8*j + s set <=> the leaf child in slot s owns a j-th triangle, j < 3; the node's
+//                       triangles are stored contiguously in (j, slot) order, so the triangle behind bit b is
+//                       tri_base + popc(tri_valid & ((1 << b) - 1)), and the candidates of an 8-bit box-hit
+//                       mask h are (h * 0x010101) & tri_valid: one IMAD instead of a bit spread)
 //       u32 reserved
 //   w2: u8 qlo_x[8], qlo_y[8]      w3: u8 qlo_z[8], qhi_x[8]      w4: u8 qhi_y[8], qhi_z[8]
 // Child box = p + q * 2^(e-127), rounded outwards by the builder (exact-arithmetic conservative).

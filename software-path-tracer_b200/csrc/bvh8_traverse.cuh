@@ -64,6 +64,7 @@ struct RayPre {
   f3 o, d, idir;
   uint32_t octinv;  // 7 ^ (direction sign octant)
   uint32_t magic;   // 0x4B000000, see byte_as_biased_float()
+  uint32_t perm_lut;  // device: shared-space byte address of the 256-entry xor_permute8(., octinv) table (0 = none)
 };
 
 __host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d, uint32_t magic = 0x4B000000u) {
@@ -78,8 +79,13 @@ __host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d, uint32_t magi
   r.idir = mk3(1.0f / dx, 1.0f / dy, 1.0f / dz);
   const uint32_t oct = (dx < 0.f ? 1u : 0u) | (dy < 0.f ? 2u : 0u) | (dz < 0.f ? 4u : 0u);
   r.octinv = 7u ^ oct;
+  r.perm_lut = 0u;
   return r;
 }
+
+// Entry distance used by the box tests: slabs are entered slightly early so that hits at exactly tnear are never
+// culled by box rounding; strictly non-zero (see the sign-bit test in intersect_node()).
+__host__ __device__ __forceinline__ float box_tmin(float tnear) { return tnear > 0.0f ? tnear * 0.5f : -1e-30f; }
 
 // Moller-Trumbore, two-sided, fixed operation order (DESIGN.md "Mesh integrator numerics").  Inside test on
 // the det-scaled barycentrics with the sign of det folded in by an exact sign-bit flip; the one IEEE division
@@ -132,8 +138,17 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   const float tmax_w = tmax * 1.000002f;
   const uint32_t magic = r.magic;
   uint32_t hits = 0;
+  // Hit <=> cmin <= cmax.  On the device the test is the SIGN BIT of (cmax - cmin) (FADD, fma pipe), shifted into
+  // the mask by one funnel shift per child: 9 alu-pipe instructions per node instead of FSETP + SEL + IADD3 = 20
+  // (the node test is alu-pipe bound, profiles/r01_notes.md).  cmin > 0 always (tmin > 0 or tiny negative, see
+  // the callers), so cmax - cmin is never -0 for cmin <= cmax, and no operand is NaN.
+#ifdef __CUDA_ARCH__
+#define PT_RECORD(BIT) hits = __funnelshift_l(__float_as_uint(cmax - cmin), hits, 1);
+#else
+#define PT_RECORD(BIT) if (cmin <= cmax) hits |= 1u << (BIT);
+#endif
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
+  for (int half = 1; half >= 0; --half) {  // children 7..0, so that the funnel leaves child k in bit k
     const uint32_t lox = half ? w2.y : w2.x, loy = half ? w2.w : w2.z, loz = half ? w3.y : w3.x;
     const uint32_t hix = half ? w3.w : w3.z, hiy = half ? w4.y : w4.x, hiz = half ? w4.w : w4.z;
     const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
@@ -150,12 +165,17 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                 \
       const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));               \
       /* empty slots (inverted boxes) may pass; imask / tri_valid keep them out */ \
-      if (cmin <= cmax) hits |= 1u << (4 * half + J);                              \
+      PT_RECORD(4 * half + J)                                                      \
     }
-    PT_CHILD(0) PT_CHILD(1) PT_CHILD(2) PT_CHILD(3)
+    PT_CHILD(3) PT_CHILD(2) PT_CHILD(1) PT_CHILD(0)
 #undef PT_CHILD
   }
+#undef PT_RECORD
+#ifdef __CUDA_ARCH__
+  return ~hits & 0xFFu;  // the funnel collected sign bits: set = miss
+#else
   return hits;
+#endif
 }
 
 // Bit s of an 8-bit mask -> bit (s ^ k): three conditional swaps (neighbours, pairs, nibbles).
@@ -167,20 +187,12 @@ __host__ __device__ __forceinline__ uint32_t xor_permute8(uint32_t x, uint32_t k
   const uint32_t c = ((x & 0x0Fu) << 4) | ((x >> 4) & 0x0Fu);
   return (k & 4u) ? c : x;
 }
-// Bit s of an 8-bit mask -> bits 3s..3s+2 of a 24-bit mask.
-__host__ __device__ __forceinline__ uint32_t spread8_to_24(uint32_t x) {
-  x = (x ^ (x << 8)) & 0x00F00Fu;
-  x = (x ^ (x << 4)) & 0x0C30C3u;
-  x = (x ^ (x << 2)) & 0x249249u;
-  return x * 7u;
-}
-
 // Stack concept: void push(uint2), uint2 pop(), bool empty().
 
 // One traversal step.  Precondition: ngroup has at least one internal child left (ngroup.y > 0x00FFFFFF).
 // Takes the highest-priority child, pushes what is left of the group, fetches that node (5 x LDG.128) and
 // tests its 8 children.  On return ngroup describes the fetched node's internal hits (bits 24..31, by
-// traversal priority slot ^ octinv) and (tri_base, tri_valid, tmask) its triangle hits (tmask bit b = candidate
+// traversal priority slot ^ octinv) and (tri_base, tri_valid, tmask) its triangle hits (tmask bit b = 8*j + slot = candidate
 // triangle tri_base + popc(tri_valid & ((1 << b) - 1))).
 template <class Stack>
 __host__ __device__ __forceinline__ void node_step(const uint4* __restrict__ nodes, const RayPre& r, float tmin_box,
@@ -196,10 +208,18 @@ __host__ __device__ __forceinline__ void node_step(const uint4* __restrict__ nod
   const uint4 w0 = PT_LDG4(np + 0), w1 = PT_LDG4(np + 1), w2 = PT_LDG4(np + 2), w3 = PT_LDG4(np + 3), w4 = PT_LDG4(np + 4);
   const uint32_t hits = intersect_node(w0, w2, w3, w4, r, tmin_box, tmax);
   const uint32_t node_imask = w0.w >> 24;
-  ngroup = make_uint2(w1.x, (xor_permute8(hits & node_imask, r.octinv) << 24) | node_imask);
+#ifdef __CUDA_ARCH__
+  // priority permutation from a shared-memory table (one LDS.U8 on the lsu pipe instead of 12 alu-pipe
+  // instructions; the kernels fill the table with xor_permute8 itself, see fill_perm_lut())
+  uint32_t prio;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(prio) : "r"(r.perm_lut + (hits & node_imask)));
+#else
+  const uint32_t prio = xor_permute8(hits & node_imask, r.octinv);
+#endif
+  ngroup = make_uint2(w1.x, (prio << 24) | node_imask);
   tri_base = w1.y;
   tri_valid = w1.z;
-  tmask = spread8_to_24(hits) & tri_valid;
+  tmask = (hits * 0x010101u) & tri_valid;  // bit 8*j + s: slot s was hit and owns a j-th triangle
 }
 
 // Tests triangle `tri`; returns true when an any-hit query is satisfied.  Closest-hit rule: smallest
@@ -239,7 +259,7 @@ __host__ __device__ __forceinline__ void bvh8_trace(const uint4* __restrict__ no
   hit.tri = 0xFFFFFFFFu;
   hit.prim = 0xFFFFFFFFu;
   // slabs are entered slightly early so hits at exactly tnear are never culled by box rounding
-  const float tmin_box = tnear * 0.5f;
+  const float tmin_box = box_tmin(tnear);
   uint2 ngroup = make_uint2(0u, 0x80000000u);  // the root, as "slot 7^octinv of a virtual parent"
   for (;;) {
     uint32_t tri_base, tri_valid, tmask;

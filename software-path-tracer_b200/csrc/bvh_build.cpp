@@ -319,7 +319,7 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     N.child_base = (uint32_t)out->nodes.size();
     N.tri_base = (uint32_t)out->tris.size();
     out->nodes.resize(out->nodes.size() + n_internal);
-    uint32_t next_internal = N.child_base, tri_off = 0;
+    uint32_t next_internal = N.child_base;
     for (int s = 0; s < 8; ++s) {
       const int i = child_in_slot[s];
       if (i < 0) continue;
@@ -327,17 +327,19 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
         N.imask |= (uint8_t)(1u << s);
         queue.push_back({ch[i].node2, next_internal++, w.depth + 1});
       } else {
-        const Node2& leaf = n2[ch[i].node2];
-        const uint32_t cnt = leaf.count;  // 1..3
-        N.tri_valid |= ((1u << cnt) - 1u) << (3 * s);
-        for (uint32_t j = 0; j < cnt; ++j) {
-          const uint32_t prim = B.perm[leaf.first + j];
-          out->tri_of_prim[prim] = (uint32_t)out->tris.size();
-          out->tris.push_back(tri[prim]);
-        }
-        tri_off += cnt;
+        const uint32_t cnt = n2[ch[i].node2].count;  // 1..3
+        for (uint32_t j = 0; j < cnt; ++j) N.tri_valid |= 1u << (8 * j + s);
       }
     }
+    // triangles of the node in (j, slot) order = ascending bit order of tri_valid
+    for (uint32_t j = 0; j < 3; ++j)
+      for (int s = 0; s < 8; ++s) {
+        if (!(N.tri_valid & (1u << (8 * j + s)))) continue;
+        const Node2& leaf = n2[ch[child_in_slot[s]].node2];
+        const uint32_t prim = B.perm[leaf.first + j];
+        out->tri_of_prim[prim] = (uint32_t)out->tris.size();
+        out->tris.push_back(tri[prim]);
+      }
     out->nodes[w.node8] = N;
   }
   if (out->max_depth > kBvh8MaxDepth) {

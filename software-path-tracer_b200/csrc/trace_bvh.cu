@@ -21,20 +21,43 @@ constexpr int kLocalStack = 32;
 constexpr int kRefillThreshold = 26;
 constexpr int kPoolRays = 64;
 
-struct DeviceStack {
-  uint2* shared_base;  // &smem[threadIdx.x], stride blockDim.x
-  uint2 local[kLocalStack];
-  int sp;
+__device__ __forceinline__ void sts64(uint32_t addr, uint2 v) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+// s_lut[k * 256 + x] = xor_permute8(x, k): child-hit mask -> traversal priority order for octant key k.
+__device__ __forceinline__ void fill_perm_lut(uint8_t* lut) {
+  for (int i = threadIdx.x; i < 8 * 256; i += kTraceBlock) lut[i] = (uint8_t)xor_permute8((uint32_t)i & 0xFFu, (uint32_t)i >> 8);
+  __syncthreads();
+}
+
+struct RegStack {
+  uint32_t sbase;  // shared-space byte address of this thread's entry 0; entries kTraceBlock * 8 bytes apart
+  uint2* local;
+  int& sp;
   __device__ __forceinline__ void push(uint2 v) {
     if (sp < kSharedStack)
-      shared_base[sp * kTraceBlock] = v;
+      sts64(sbase + (uint32_t)sp * (kTraceBlock * 8u), v);
     else if (sp < kSharedStack + kLocalStack)
       local[sp - kSharedStack] = v;
-    ++sp;  // deeper than the builder's kBvh8MaxDepth bound cannot happen
+    ++sp;
   }
   __device__ __forceinline__ uint2 pop() {
     --sp;
-    return sp < kSharedStack ? shared_base[sp * kTraceBlock] : local[sp - kSharedStack];
+    return sp < kSharedStack ? lds64(sbase + (uint32_t)sp * (kTraceBlock * 8u)) : local[sp - kSharedStack];
   }
   __device__ __forceinline__ bool empty() const { return sp == 0; }
 };
@@ -48,11 +71,14 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
                  uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
                  const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold, const uint32_t magic) {
   __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
+  __shared__ uint8_t s_lut[8 * 256];
+  fill_perm_lut(s_lut);
+  const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(s_lut);
   const uint32_t n = *count_ptr;
   const unsigned lane = threadIdx.x & 31u;
-  DeviceStack stack;
-  stack.shared_base = s_stack + threadIdx.x;
-  stack.sp = 0;
+  uint2 lstack[kLocalStack];
+  int sp = 0;
+  RegStack stack{(uint32_t)__cvta_generic_to_shared(s_stack) + threadIdx.x * 8u, lstack, sp};
 
   bool active = false, drained = false;
   uint32_t pool_next = 0, pool_left = 0;  // warp-uniform
@@ -87,6 +113,7 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
           path = queue[i];
           const float4 o4 = ray_o[path], d4 = ray_d[path];
           r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), magic);
+          r.perm_lut = lut_base + r.octinv * 256u;
           if (kAnyHit) {
             tnear = d4.w;  // shadow rays: {o, tmax}, {d, tnear}
             tmax = o4.w;
@@ -94,12 +121,12 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
             tnear = o4.w;
             tmax = d4.w;
           }
-          tmin_box = tnear * 0.5f;
+          tmin_box = box_tmin(tnear);
           hit.t = tmax;
           hit.tri = 0xFFFFFFFFu;
           hit.prim = 0xFFFFFFFFu;
           ngroup = make_uint2(0u, 0x80000000u);
-          stack.sp = 0;
+          sp = 0;
           active = true;
         }
       }
@@ -165,6 +192,178 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
 }
 
+
+// ---- v2: deferred triangle tests ---------------------------------------------------------------------------
+// profiles/r01_notes.md: in the kernel above the triangle tests of one iteration run with ~4 of 32 lanes (only
+// ~20 % of lanes find candidates in a given node step) and cost 27 % of the issue slots.  Here a lane only
+// RECORDS its candidate triangles (4-byte leaf-order indices, per-lane list in shared memory) and keeps
+// traversing; the warp runs a triangle phase when enough lanes have something pending (vote), when a list is
+// nearly full, or before lanes are refilled.  The closest-hit rule (smallest t, ties to the smallest caller
+// index) does not depend on the order of the tests, so the result is bit-identical; the price is that hit.t
+// shrinks a step or two later (slightly more node steps).
+// Also: stack pointer and list length live in registers and the shared-memory stack is addressed with
+// st.shared/ld.shared (the struct above made ptxas keep `sp` in local memory and use generic stores).
+constexpr int kPendCap = 8;
+
+template <bool kAnyHit, bool kCount, int kBlocksPerSM>
+__global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
+    trace_kernel_v2(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
+                    const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
+                    uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
+                    const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold,
+                    const uint32_t magic, const int tri_min, const int tri_round_min) {
+  __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
+  __shared__ uint32_t s_pend[kPendCap * kTraceBlock];
+  __shared__ uint8_t s_lut[8 * 256];
+  fill_perm_lut(s_lut);
+  const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(s_lut);
+  const uint32_t n = *count_ptr;
+  const unsigned lane = threadIdx.x & 31u;
+  uint2 lstack[kLocalStack];
+  int sp = 0;
+  RegStack stack{(uint32_t)__cvta_generic_to_shared(s_stack) + threadIdx.x * 8u, lstack, sp};
+  const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_pend) + threadIdx.x * 4u;
+  int cnt = 0;  // pending candidate triangles of this lane
+
+  bool active = false;  // lane owns a ray
+  bool trav = false;    // ... and still has nodes to visit
+  bool drained = false;
+  uint32_t pool_next = 0, pool_left = 0;  // warp-uniform
+  uint32_t path = 0;
+  RayPre r;
+  float tnear = 0.f, tmax = 0.f, tmin_box = 0.f;
+  TraceHit hit;
+  uint2 ngroup = make_uint2(0u, 0u);
+  uint32_t n_nodes = 0, n_tris = 0;
+
+  for (;;) {
+    // ---- refill idle lanes (warp-synchronous), as in trace_kernel ----
+    const unsigned idle = __ballot_sync(0xffffffffu, !active);
+    if (idle && !drained) {
+      const uint32_t want = (uint32_t)__popc(idle);
+      if (pool_left < want && pool_left == 0u) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(work_counter, (uint32_t)kPoolRays);
+        pool_next = __shfl_sync(0xffffffffu, base, 0);
+        pool_left = pool_next < n ? min((uint32_t)kPoolRays, n - pool_next) : 0u;
+        if (pool_left == 0u) drained = true;
+      }
+      if (!active) {
+        const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        if (rank < pool_left) {
+          path = queue[pool_next + rank];
+          const float4 o4 = ray_o[path], d4 = ray_d[path];
+          r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), magic);
+          r.perm_lut = lut_base + r.octinv * 256u;
+          if (kAnyHit) {
+            tnear = d4.w;  // shadow rays: {o, tmax}, {d, tnear}
+            tmax = o4.w;
+          } else {
+            tnear = o4.w;
+            tmax = d4.w;
+          }
+          tmin_box = box_tmin(tnear);
+          hit.t = tmax;
+          hit.tri = 0xFFFFFFFFu;
+          hit.prim = 0xFFFFFFFFu;
+          ngroup = make_uint2(0u, 0x80000000u);
+          sp = 0;
+          cnt = 0;
+          active = true;
+          trav = true;
+        }
+      }
+      const uint32_t served = min(want, pool_left);
+      pool_next += served;
+      pool_left -= served;
+    }
+    if (__ballot_sync(0xffffffffu, active) == 0u) break;
+
+    for (;;) {
+      if (trav) {
+        uint32_t tri_base, tri_valid, tmask;
+        node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tri_valid, tmask);
+        if (kCount) ++n_nodes;
+        while (tmask) {  // record the candidates; tested later with the rest of the warp
+          const int ti = pt_bfind(tmask);
+          tmask &= ~(1u << ti);
+          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & ((1u << ti) - 1u));
+          if (cnt < kPendCap) {
+            sts32(pbase + (uint32_t)cnt * (kTraceBlock * 4u), tri);
+            ++cnt;
+          } else {  // list full (a node can offer up to 24 candidates): test right away
+            if (kCount) ++n_tris;
+            if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {
+              trav = false;
+              cnt = 0;
+              tmask = 0u;
+            }
+          }
+        }
+        if (trav && ngroup.y <= 0x00FFFFFFu) {
+          if (sp == 0)
+            trav = false;
+          else
+            ngroup = stack.pop();
+        }
+      }
+      const unsigned pend = __ballot_sync(0xffffffffu, cnt > 0);
+      const unsigned travm = __ballot_sync(0xffffffffu, trav);
+      const int n_trav = __popc(travm);
+      const bool leaving = (!drained && n_trav < refill_threshold) || travm == 0u;
+      if (pend) {
+        const int n_pend = __popc(pend);
+        const bool full = __any_sync(0xffffffffu, cnt > kPendCap - 3);
+        if (leaving || full || n_pend >= tri_min || n_pend >= n_trav) {
+          const int round_min = leaving ? 1 : tri_round_min;
+          for (;;) {
+            if (cnt > 0) {
+              --cnt;
+              const uint32_t tri = lds32(pbase + (uint32_t)cnt * (kTraceBlock * 4u));
+              if (kCount) ++n_tris;
+              if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {  // any-hit satisfied: the ray is done
+                cnt = 0;
+                trav = false;
+              }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, cnt > 0)) < round_min) break;
+          }
+        }
+      }
+      if (active && !trav && cnt == 0) {
+        if (kAnyHit) {
+          if (hit.tri == 0xFFFFFFFFu) {  // unoccluded: add the light sample (path-private slot, no atomics)
+            float4 l = L[path];
+            const float4 c = contrib[path];
+            l.x += c.x;
+            l.y += c.y;
+            l.z += c.z;
+            L[path] = l;
+          }
+        } else {
+          hit_out[path] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
+        }
+        active = false;
+      }
+      if (leaving) break;
+    }
+  }
+  if (kCount) {
+    const uint64_t wn = warp_sum_u32(n_nodes), wt = warp_sum_u32(n_tris);
+    if (lane == 0) {
+      atomicAdd(&stats[kCntNodes], (unsigned long long)wn);
+      atomicAdd(&stats[kCntTris], (unsigned long long)wt);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
+}
+
+int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  const int x = e ? atoi(e) : dflt;
+  return x < lo ? lo : (x > hi ? hi : x);
+}
+
 // Tuning knob (profiles/r01_notes.md): lanes are refilled when fewer than this many of a warp's 32 are busy.
 int refill_threshold() {
   static const int v = [] {
@@ -180,7 +379,7 @@ int trace_blocks_per_sm() {
   static const int v = [] {
     const char* e = getenv("CUDAPT_TRACE_BLOCKS");
     const int x = e ? atoi(e) : kTraceBlocksPerSM;
-    return (x >= 5 && x <= 12) ? x : kTraceBlocksPerSM;
+    return (x == 6 || x == 8 || x == 9) ? x : kTraceBlocksPerSM;
   }();
   return v;
 }
@@ -192,21 +391,24 @@ cudaError_t launch_trace(const PassParams& p, const float4* ro, const float4* rd
   const int bps = trace_blocks_per_sm();
   const dim3 grid(sm_count * bps), block(kTraceBlock);
   const int thr = refill_threshold();
-#define PT_LAUNCH(B, C)                                                                                                 \
-  trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L, contrib, \
-                                                     p.counters, thr, 0x4B000000u)
+  static const int defer = env_int("CUDAPT_TRACE_DEFER", 1, 0, 1);
+  static const int tri_min = env_int("CUDAPT_TRI_MIN", 12, 1, 32);
+  static const int tri_round_min = env_int("CUDAPT_TRI_ROUND_MIN", 6, 1, 32);
+#define PT_LAUNCH(B, C)                                                                                                    \
+  if (defer)                                                                                                               \
+    trace_kernel_v2<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L,  \
+                                                          contrib, p.counters, thr, 0x4B000000u, tri_min, tri_round_min);  \
+  else                                                                                                                     \
+    trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L,     \
+                                                       contrib, p.counters, thr, 0x4B000000u)
 #define PT_PICK(B)          \
   if (counting)             \
     PT_LAUNCH(B, true);     \
   else                      \
     PT_LAUNCH(B, false)
   switch (bps) {
-    case 5: PT_PICK(5); break;
     case 6: PT_PICK(6); break;
-    case 7: PT_PICK(7); break;
     case 9: PT_PICK(9); break;
-    case 10: PT_PICK(10); break;
-    case 12: PT_PICK(12); break;
     default: PT_PICK(8); break;
   }
 #undef PT_PICK
