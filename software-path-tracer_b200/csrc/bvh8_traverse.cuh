@@ -87,23 +87,28 @@ __host__ __device__ __forceinline__ RayPre prepare_ray(f3 o, f3 d, uint32_t magi
 // culled by box rounding; strictly non-zero (see the sign-bit test in intersect_node()).
 __host__ __device__ __forceinline__ float box_tmin(float tnear) { return tnear > 0.0f ? tnear * 0.5f : -1e-30f; }
 
-// Moller-Trumbore, two-sided, fixed operation order (DESIGN.md "Mesh integrator numerics").  Inside test on
+// Moller-Trumbore, two-sided, fixed operation order with FUSED products (explicit fmaf: one rounding each, the
+// same nesting as oracle/twin/twin.cpp; DESIGN.md "Mesh integrator numerics").  Inside test on
 // the det-scaled barycentrics with the sign of det folded in by an exact sign-bit flip; the one IEEE division
 // (t = (e2 . q) / det) is only reached by candidates that are inside, so the common reject paths cost ~25 and
 // ~45 instructions instead of ~90 (profiles/r01_notes.md: triangle tests ran at 4/32 lanes, 27 % of issue).
+__host__ __device__ __forceinline__ float dot3f(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__host__ __device__ __forceinline__ f3 cross3f(f3 a, f3 b) {
+  return mk3(fmaf(a.y, b.z, -(b.y * a.z)), fmaf(a.z, b.x, -(b.z * a.x)), fmaf(a.x, b.y, -(b.x * a.y)));
+}
 __host__ __device__ __forceinline__ bool tri_test(f3 v0, f3 e1, f3 e2, f3 o, f3 d, float& t) {
-  const f3 pv = cross3(d, e2);
-  const float det = dot3(e1, pv);
+  const f3 pv = cross3f(d, e2);
+  const float det = dot3f(e1, pv);
   if (det == 0.0f) return false;
   const uint32_t sb = pt_as_uint(det) & 0x80000000u;
   const float adet = pt_as_float(pt_as_uint(det) ^ sb);
   const f3 tv = o - v0;
-  const float u = pt_as_float(pt_as_uint(dot3(tv, pv)) ^ sb);
+  const float u = pt_as_float(pt_as_uint(dot3f(tv, pv)) ^ sb);
   if (!(u >= 0.0f && u <= adet)) return false;
-  const f3 qv = cross3(tv, e1);
-  const float v = pt_as_float(pt_as_uint(dot3(d, qv)) ^ sb);
+  const f3 qv = cross3f(tv, e1);
+  const float v = pt_as_float(pt_as_uint(dot3f(d, qv)) ^ sb);
   if (!(v >= 0.0f && (u + v) <= adet)) return false;
-  t = dot3(e2, qv) / det;
+  t = dot3f(e2, qv) / det;
   return true;
 }
 

@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <limits>
@@ -55,6 +56,8 @@ struct Builder {
   std::vector<Node2> nodes;
   std::atomic<uint32_t> next{1};
   std::atomic<int> spare{0};
+  uint32_t leaf_max = 3;   // triangles per leaf (<= 3: the node format has three tri_valid planes)
+  float trav_cost = 0.8f;  // SAH cost of one more box test relative to one triangle test
 
   void build(uint32_t node, uint32_t begin, uint32_t end) {
     Box box, cbox;
@@ -109,11 +112,11 @@ struct Builder {
     }
     uint32_t mid;
     if (best_axis < 0) {
-      if (count <= 3) return make_leaf();
+      if (count <= leaf_max) return make_leaf();
       mid = begin + count / 2;  // coincident centroids: split the index range
     } else {
-      const float split_cost = 0.8f + best_cost / std::max(box.area(), 1e-30f);
-      if (count <= 3 && split_cost >= (float)count) return make_leaf();
+      const float split_cost = trav_cost + best_cost / std::max(box.area(), 1e-30f);
+      if (count <= leaf_max && split_cost >= (float)count) return make_leaf();
       const float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
       const float scale = (float)kBins / ext;
       const float lo = cbox.lo[best_axis];
@@ -193,6 +196,8 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
   for (uint32_t i = 0; i < nt; ++i) B.perm[i] = i;
   B.nodes.resize(2 * (size_t)nt + 1);
   B.spare.store(std::max(threads, 1) - 1);
+  if (const char* e = std::getenv("CUDAPT_BVH_LEAF_MAX")) B.leaf_max = (uint32_t)std::min(std::max(std::atoi(e), 1), 3);
+  if (const char* e = std::getenv("CUDAPT_BVH_TRAV_COST")) B.trav_cost = (float)std::atof(e);
   B.build(0, 0, nt);
   const std::vector<Node2>& n2 = B.nodes;
 

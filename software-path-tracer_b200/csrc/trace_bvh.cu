@@ -146,10 +146,12 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
         if (kCount) ++n_nodes;
         bool finished = false;
         while (tmask) {
-          const int ti = pt_bfind(tmask);
-          tmask &= ~(1u << ti);
+          // lowest candidate first (the order of the tests does not matter): isolating the lowest set bit is
+          // two alu instructions, against FLO (xu pipe) + shift + mask for the highest
+          const uint32_t low = tmask & (0u - tmask);
+          tmask ^= low;
           if (kCount) ++n_tris;
-          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & ((1u << ti) - 1u));
+          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & (low - 1u));
           if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {
             finished = true;
             break;
@@ -193,171 +195,6 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
 }
 
 
-// ---- v2: deferred triangle tests ---------------------------------------------------------------------------
-// profiles/r01_notes.md: in the kernel above the triangle tests of one iteration run with ~4 of 32 lanes (only
-// ~20 % of lanes find candidates in a given node step) and cost 27 % of the issue slots.  Here a lane only
-// RECORDS its candidate triangles (4-byte leaf-order indices, per-lane list in shared memory) and keeps
-// traversing; the warp runs a triangle phase when enough lanes have something pending (vote), when a list is
-// nearly full, or before lanes are refilled.  The closest-hit rule (smallest t, ties to the smallest caller
-// index) does not depend on the order of the tests, so the result is bit-identical; the price is that hit.t
-// shrinks a step or two later (slightly more node steps).
-// Also: stack pointer and list length live in registers and the shared-memory stack is addressed with
-// st.shared/ld.shared (the struct above made ptxas keep `sp` in local memory and use generic stores).
-constexpr int kPendCap = 8;
-
-template <bool kAnyHit, bool kCount, int kBlocksPerSM>
-__global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
-    trace_kernel_v2(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float4* __restrict__ ray_o,
-                    const float4* __restrict__ ray_d, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count_ptr,
-                    uint32_t* __restrict__ work_counter, uint2* __restrict__ hit_out, float4* __restrict__ L,
-                    const float4* __restrict__ contrib, unsigned long long* __restrict__ stats, const int refill_threshold,
-                    const uint32_t magic, const int tri_min, const int tri_round_min) {
-  __shared__ uint2 s_stack[kSharedStack * kTraceBlock];
-  __shared__ uint32_t s_pend[kPendCap * kTraceBlock];
-  __shared__ uint8_t s_lut[8 * 256];
-  fill_perm_lut(s_lut);
-  const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(s_lut);
-  const uint32_t n = *count_ptr;
-  const unsigned lane = threadIdx.x & 31u;
-  uint2 lstack[kLocalStack];
-  int sp = 0;
-  RegStack stack{(uint32_t)__cvta_generic_to_shared(s_stack) + threadIdx.x * 8u, lstack, sp};
-  const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_pend) + threadIdx.x * 4u;
-  int cnt = 0;  // pending candidate triangles of this lane
-
-  bool active = false;  // lane owns a ray
-  bool trav = false;    // ... and still has nodes to visit
-  bool drained = false;
-  uint32_t pool_next = 0, pool_left = 0;  // warp-uniform
-  uint32_t path = 0;
-  RayPre r;
-  float tnear = 0.f, tmax = 0.f, tmin_box = 0.f;
-  TraceHit hit;
-  uint2 ngroup = make_uint2(0u, 0u);
-  uint32_t n_nodes = 0, n_tris = 0;
-
-  for (;;) {
-    // ---- refill idle lanes (warp-synchronous), as in trace_kernel ----
-    const unsigned idle = __ballot_sync(0xffffffffu, !active);
-    if (idle && !drained) {
-      const uint32_t want = (uint32_t)__popc(idle);
-      if (pool_left < want && pool_left == 0u) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(work_counter, (uint32_t)kPoolRays);
-        pool_next = __shfl_sync(0xffffffffu, base, 0);
-        pool_left = pool_next < n ? min((uint32_t)kPoolRays, n - pool_next) : 0u;
-        if (pool_left == 0u) drained = true;
-      }
-      if (!active) {
-        const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
-        if (rank < pool_left) {
-          path = queue[pool_next + rank];
-          const float4 o4 = ray_o[path], d4 = ray_d[path];
-          r = prepare_ray(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), magic);
-          r.perm_lut = lut_base + r.octinv * 256u;
-          if (kAnyHit) {
-            tnear = d4.w;  // shadow rays: {o, tmax}, {d, tnear}
-            tmax = o4.w;
-          } else {
-            tnear = o4.w;
-            tmax = d4.w;
-          }
-          tmin_box = box_tmin(tnear);
-          hit.t = tmax;
-          hit.tri = 0xFFFFFFFFu;
-          hit.prim = 0xFFFFFFFFu;
-          ngroup = make_uint2(0u, 0x80000000u);
-          sp = 0;
-          cnt = 0;
-          active = true;
-          trav = true;
-        }
-      }
-      const uint32_t served = min(want, pool_left);
-      pool_next += served;
-      pool_left -= served;
-    }
-    if (__ballot_sync(0xffffffffu, active) == 0u) break;
-
-    for (;;) {
-      if (trav) {
-        uint32_t tri_base, tri_valid, tmask;
-        node_step(nodes, r, tmin_box, kAnyHit ? tmax : hit.t, ngroup, stack, tri_base, tri_valid, tmask);
-        if (kCount) ++n_nodes;
-        while (tmask) {  // record the candidates; tested later with the rest of the warp
-          const int ti = pt_bfind(tmask);
-          tmask &= ~(1u << ti);
-          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & ((1u << ti) - 1u));
-          if (cnt < kPendCap) {
-            sts32(pbase + (uint32_t)cnt * (kTraceBlock * 4u), tri);
-            ++cnt;
-          } else {  // list full (a node can offer up to 24 candidates): test right away
-            if (kCount) ++n_tris;
-            if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {
-              trav = false;
-              cnt = 0;
-              tmask = 0u;
-            }
-          }
-        }
-        if (trav && ngroup.y <= 0x00FFFFFFu) {
-          if (sp == 0)
-            trav = false;
-          else
-            ngroup = stack.pop();
-        }
-      }
-      const unsigned pend = __ballot_sync(0xffffffffu, cnt > 0);
-      const unsigned travm = __ballot_sync(0xffffffffu, trav);
-      const int n_trav = __popc(travm);
-      const bool leaving = (!drained && n_trav < refill_threshold) || travm == 0u;
-      if (pend) {
-        const int n_pend = __popc(pend);
-        const bool full = __any_sync(0xffffffffu, cnt > kPendCap - 3);
-        if (leaving || full || n_pend >= tri_min || n_pend >= n_trav) {
-          const int round_min = leaving ? 1 : tri_round_min;
-          for (;;) {
-            if (cnt > 0) {
-              --cnt;
-              const uint32_t tri = lds32(pbase + (uint32_t)cnt * (kTraceBlock * 4u));
-              if (kCount) ++n_tris;
-              if (tri_step<kAnyHit>(tris, tri, r, tnear, tmax, hit)) {  // any-hit satisfied: the ray is done
-                cnt = 0;
-                trav = false;
-              }
-            }
-            if (__popc(__ballot_sync(0xffffffffu, cnt > 0)) < round_min) break;
-          }
-        }
-      }
-      if (active && !trav && cnt == 0) {
-        if (kAnyHit) {
-          if (hit.tri == 0xFFFFFFFFu) {  // unoccluded: add the light sample (path-private slot, no atomics)
-            float4 l = L[path];
-            const float4 c = contrib[path];
-            l.x += c.x;
-            l.y += c.y;
-            l.z += c.z;
-            L[path] = l;
-          }
-        } else {
-          hit_out[path] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
-        }
-        active = false;
-      }
-      if (leaving) break;
-    }
-  }
-  if (kCount) {
-    const uint64_t wn = warp_sum_u32(n_nodes), wt = warp_sum_u32(n_tris);
-    if (lane == 0) {
-      atomicAdd(&stats[kCntNodes], (unsigned long long)wn);
-      atomicAdd(&stats[kCntTris], (unsigned long long)wt);
-    }
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
-}
-
 int env_int(const char* name, int dflt, int lo, int hi) {
   const char* e = getenv(name);
   const int x = e ? atoi(e) : dflt;
@@ -391,16 +228,9 @@ cudaError_t launch_trace(const PassParams& p, const float4* ro, const float4* rd
   const int bps = trace_blocks_per_sm();
   const dim3 grid(sm_count * bps), block(kTraceBlock);
   const int thr = refill_threshold();
-  static const int defer = env_int("CUDAPT_TRACE_DEFER", 1, 0, 1);
-  static const int tri_min = env_int("CUDAPT_TRI_MIN", 12, 1, 32);
-  static const int tri_round_min = env_int("CUDAPT_TRI_ROUND_MIN", 6, 1, 32);
-#define PT_LAUNCH(B, C)                                                                                                    \
-  if (defer)                                                                                                               \
-    trace_kernel_v2<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L,  \
-                                                          contrib, p.counters, thr, 0x4B000000u, tri_min, tri_round_min);  \
-  else                                                                                                                     \
-    trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L,     \
-                                                       contrib, p.counters, thr, 0x4B000000u)
+#define PT_LAUNCH(B, C)                                                                                                 \
+  trace_kernel<kAnyHit, C, B><<<grid, block, 0, s>>>(p.scene.nodes, p.scene.tris, ro, rd, queue, count, work, hit, L, contrib, \
+                                                     p.counters, thr, 0x4B000000u)
 #define PT_PICK(B)          \
   if (counting)             \
     PT_LAUNCH(B, true);     \
