@@ -9,3 +9,4 @@ print('value',round(d['value'],1),'ms',round(d['ms_per_step'],2),'trace_ms/launc
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 run A=1
 run CUDAPT_TRACE_BLOCKS=9
+run CUDAPT_TRACE_BLOCKS=6
