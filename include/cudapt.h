@@ -135,6 +135,15 @@ int cudapt_build_accel(cudapt_ctx* ctx);
  * Scene::hasChanges(), CPT.cpp:122-131,156-160). */
 int cudapt_reupload_scene(cudapt_ctx* ctx);
 
+/* Environment map replacing the procedural sky on a miss (reference anchor: the commented-out
+ * Scene::setEnvironmentMap, libs/render/src/Scene.cpp:124-169, and the SkyBox of Scene.h:268-278).  rgb is a
+ * size x size OCTAHEDRAL map, row-major float3 texels, pole axis +Y: direction d maps to p = (d.x, d.z) /
+ * (|d.x|+|d.y|+|d.z|), lower hemisphere folded outwards, texel coordinates (p*0.5+0.5)*size - 0.5, bilinear,
+ * clamped.  (Octahedral rather than lat-long so that the lookup needs no atan2/acos and the CPU oracle
+ * matches bit for bit.)  Both integrators use it; sky_scale still multiplies it.  rgb = NULL or size = 0 restores
+ * the reference's procedural sky (CPT.cpp:286-292).  Restarts accumulation. */
+int cudapt_upload_environment(cudapt_ctx* ctx, const float* rgb, uint32_t size);
+
 /* ---- progressive rendering: render(), CPT.cpp:43-85 ------------------------------------------------ */
 /* Zero the accumulation buffer, frame count = 0 (CPT.cpp:151-154). */
 int cudapt_reset(cudapt_ctx* ctx);
@@ -146,6 +155,30 @@ int cudapt_synchronize(cudapt_ctx* ctx);
 /* ---- read-back: get_render_result(), CPT.cpp:87-117 + Color.h:7-10 --------------------------------- */
 /* accum/frame_count -> clamp[0,1] -> (uint8)(c*255) -> R<<24|G<<16|B<<8|A, W*H words, row 0 on top. */
 int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out);
+/* Post-process stage applied by cudapt_resolve_rgba8 between the division by frame_count and the 8-bit pack
+ * (SURVEY.md 8f-2).  Reference anchors: the exposure multiply commented out at CPT.cpp:101-104 with
+ * RenderSettings::getExposure()/getAutoExposure()/getTargetLuminance() (Types.h:57-58,67-69), and the
+ * acesTonemap / reinhardTonemap / linearToSRGB declarations of libs/render/src/utils/Math.h:25-34 (never
+ * defined there).  The defaults (exposure 1, no tone map, linear, no auto-exposure) reproduce CPT.cpp:87-117
+ * bit for bit.  Order: c = accum/frames; c *= exposure (auto: target_luminance / exp(mean log luminance));
+ * tone map; clamp[0,1]; optional sRGB OETF; (uint8)(c*255).  Alpha is never touched. */
+typedef enum cudapt_tonemap { CUDAPT_TONEMAP_NONE = 0, CUDAPT_TONEMAP_REINHARD = 1, CUDAPT_TONEMAP_ACES = 2 } cudapt_tonemap;
+typedef struct cudapt_postprocess {
+  float exposure;          /* default 1.0f (RenderSettings::m_exposure, Types.h:87) */
+  int32_t tonemap;         /* cudapt_tonemap, default NONE */
+  int32_t srgb;            /* default 0: linear output as the reference */
+  int32_t auto_exposure;   /* default 0 (Types.h:88); 1 = exposure from the log-average luminance, on the device */
+  float target_luminance;  /* default 0.18f (Types.h:89) */
+} cudapt_postprocess;
+void cudapt_default_postprocess(cudapt_postprocess* pp);
+int cudapt_set_postprocess(cudapt_ctx* ctx, const cudapt_postprocess* pp);
+/* The exposure multiplier the last cudapt_resolve_rgba8 used (the auto-exposure result when enabled). */
+int cudapt_get_exposure(cudapt_ctx* ctx, float* exposure);
+/* Image writer for headless use (the reference only displays through SDL, App.cpp:236-238):
+ * ".ppm" = binary P6 of the post-processed 8-bit image, ".pfm" = float RGB accum/frame_count (bottom row first,
+ * little endian), chosen by the file extension. */
+int cudapt_write_image(cudapt_ctx* ctx, const char* path);
+
 /* Float accumulation (private m_accumulation_buffer, CPT.h:72): 4*W*H floats RGBA, and the frame count. */
 int cudapt_read_accum(cudapt_ctx* ctx, float* host_out, uint32_t* frame_count);
 /* Restore a previously read state (checkpoint/resume, merging partial renders). */

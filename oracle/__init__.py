@@ -121,7 +121,7 @@ class TwinParams(ctypes.Structure):
         ("cam_origin", ctypes.c_float * 3), ("cam_right", ctypes.c_float * 3), ("cam_up", ctypes.c_float * 3),
         ("cam_forward", ctypes.c_float * 3), ("cam_tan_half_fov", ctypes.c_float), ("threads", ctypes.c_int32),
         ("part_rank", ctypes.c_int32), ("part_world", ctypes.c_int32), ("tile_w", ctypes.c_int32),
-        ("tile_h", ctypes.c_int32),
+        ("tile_h", ctypes.c_int32), ("env_rgb", ctypes.c_void_p), ("env_size", ctypes.c_int32),
     ]
 
 
@@ -174,6 +174,12 @@ def twin_params(width: int, height: int, **kw) -> TwinParams:
     for k, v in kw.items():
         if k in ("cam_origin", "cam_right", "cam_up", "cam_forward"):
             setattr(p, k, (ctypes.c_float * 3)(*[float(x) for x in v]))
+        elif k == "env":  # octahedral environment map, (n, n, 3) float32; kept alive on the params object
+            env = np.ascontiguousarray(v, np.float32)
+            assert env.ndim == 3 and env.shape[0] == env.shape[1] and env.shape[2] == 3
+            p._env_keepalive = env
+            p.env_rgb = env.ctypes.data
+            p.env_size = env.shape[0]
         else:
             if not hasattr(p, k):
                 raise AttributeError(k)
@@ -242,6 +248,41 @@ def twin_resolve_rgba8(accum: np.ndarray, frame_count: int) -> np.ndarray:
     out = np.zeros(accum.shape[:-1], np.uint32)
     _twin().twin_resolve_rgba8(_ptr(accum), n, frame_count, _ptr(out))
     return out
+
+
+def post_resolve_rgba8(accum: np.ndarray, frame_count: int, exposure: float = 1.0, tonemap: int = 0, srgb: int = 0,
+                       auto_exposure: int = 0, target_luminance: float = 0.18):
+    """Resolve with the post-process stage restated in numpy float32: every binary operation below is
+    one IEEE-754 binary32 operation (numpy does not contract a*b+c), in the order of csrc/post.cu.  Reference
+    anchors: CPT.cpp:87-117 (resolve), :101-104 (exposure), Types.h:87-89 (defaults), utils/Math.h:29-34 (declared
+    operators).  Returns (rgba8 words, exposure used).  With the defaults it equals twin_resolve_rgba8."""
+    f32 = np.float32
+    a = np.ascontiguousarray(accum, f32).reshape(-1, 4)
+    fc = f32(frame_count)
+    c = a[:, :3] / fc
+    e = f32(exposure)
+    if auto_exposure:
+        lum = (f32(0.2126) * c[:, 0] + f32(0.7152) * c[:, 1]) + f32(0.0722) * c[:, 2]
+        mean_log = f32(np.log(np.maximum(lum, f32(1e-4))).astype(np.float64).sum() / lum.size)
+        e = f32(target_luminance) / np.exp(mean_log, dtype=f32)
+    v = c * e
+    if tonemap == 1:
+        v = v / (f32(1.0) + v)
+    elif tonemap == 2:
+        num = v * (f32(2.51) * v + f32(0.03))
+        den = v * (f32(2.43) * v + f32(0.59)) + f32(0.14)
+        v = num / den
+    v = np.where(v < 0, f32(0), np.where(v > 1, f32(1), v)).astype(f32)
+    if srgb:
+        enc = f32(1.055) * np.power(v, f32(1.0) / f32(2.4), dtype=f32) - f32(0.055)
+        v = np.where(v <= f32(0.0031308), f32(12.92) * v, enc).astype(f32)
+        v = np.where(v < 0, f32(0), np.where(v > 1, f32(1), v)).astype(f32)
+    al = a[:, 3] / fc
+    al = np.where(al < 0, f32(0), np.where(al > 1, f32(1), al)).astype(f32)
+    b = (v * f32(255.0)).astype(np.uint32) & 0xFF  # truncation, CPT.cpp:112
+    ab = (al * f32(255.0)).astype(np.uint32) & 0xFF
+    out = (b[:, 0] << 24) | (b[:, 1] << 16) | (b[:, 2] << 8) | ab  # Color.h:9
+    return out.astype(np.uint32).reshape(np.asarray(accum).shape[:-1]), float(e)
 
 
 def pcg_stream(x, y, width, frame, n):

@@ -147,6 +147,34 @@ inline V3 sample_sky(V3 d) {
   return v3(1.0f * omt + 0.5f * t, 1.0f * omt + 0.7f * t, 1.0f * omt + 1.0f * t);
 }
 
+// Miss radiance: procedural sky, or the bilinear octahedral environment lookup specified in include/cudapt.h
+// (cudapt_upload_environment) -- only + - * / and comparisons, same order as csrc/common.cuh sky_radiance().
+inline V3 sky_radiance(const twin_params& p, V3 d) {
+  if (p.env_rgb == nullptr || p.env_size <= 0) return sample_sky(d);
+  const float s = (fabsf(d.x) + fabsf(d.y)) + fabsf(d.z);
+  float px = d.x / s, pz = d.z / s;
+  if (d.y < 0.0f) {
+    const float fx = 1.0f - fabsf(pz), fz = 1.0f - fabsf(px);
+    px = d.x < 0.0f ? -fx : fx;
+    pz = d.z < 0.0f ? -fz : fz;
+  }
+  const uint32_t N = (uint32_t)p.env_size;
+  const float n = (float)N, hi = (float)(N - 1u);
+  float x = (px * 0.5f + 0.5f) * n - 0.5f, y = (pz * 0.5f + 0.5f) * n - 0.5f;
+  x = x < 0.0f ? 0.0f : (x > hi ? hi : x);
+  y = y < 0.0f ? 0.0f : (y > hi ? hi : y);
+  const uint32_t x0 = (uint32_t)x, y0 = (uint32_t)y;
+  const uint32_t x1 = x0 + 1u < N ? x0 + 1u : x0, y1 = y0 + 1u < N ? y0 + 1u : y0;
+  const float fx = x - (float)x0, fy = y - (float)y0, gx = 1.0f - fx, gy = 1.0f - fy;
+  const float* c00 = p.env_rgb + 3 * ((size_t)y0 * N + x0);
+  const float* c10 = p.env_rgb + 3 * ((size_t)y0 * N + x1);
+  const float* c01 = p.env_rgb + 3 * ((size_t)y1 * N + x0);
+  const float* c11 = p.env_rgb + 3 * ((size_t)y1 * N + x1);
+  return v3((c00[0] * gx + c10[0] * fx) * gy + (c01[0] * gx + c11[0] * fx) * fy,
+            (c00[1] * gx + c10[1] * fx) * gy + (c01[1] * gx + c11[1] * fx) * fy,
+            (c00[2] * gx + c10[2] * fx) * gy + (c01[2] * gx + c11[2] * fx) * fy);
+}
+
 inline bool owns_pixel(const twin_params& p, uint32_t x, uint32_t y) {
   if (p.part_world <= 1) return true;
   const uint32_t tx = x / (uint32_t)p.tile_w, ty = y / (uint32_t)p.tile_h;
@@ -224,7 +252,7 @@ V3 trace_spheres(const twin_params& p, const float* sph, int n, V3 o, V3 d, uint
       *first_t = h.t;
     }
     if (h.idx < 0) {
-      const V3 sky = sample_sky(d);
+      const V3 sky = sky_radiance(p, d);
       acc = acc + thr * (p.sky_scale == 1.0f ? sky : sky * p.sky_scale);
       break;
     }
@@ -497,7 +525,7 @@ V3 trace_mesh(const twin_params& p, const Mesh& m, V3 o, V3 d, uint32_t pixel, u
       *first_t = h.t;
     }
     if (h.prim < 0) {
-      const V3 sky = sample_sky(d);
+      const V3 sky = sky_radiance(p, d);
       L = L + thr * (sky * p.sky_scale);
       break;
     }

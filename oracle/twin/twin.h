@@ -37,6 +37,10 @@ typedef struct twin_params {
   int32_t threads;      /* host threads; <= 0 = all */
   /* interleaved-tile partition (mirrors cudapt_set_tile_partition); world <= 1 disables */
   int32_t part_rank, part_world, tile_w, tile_h;
+  /* octahedral environment map (mirrors cudapt_upload_environment): env_size x env_size float3 texels, or NULL =
+   * the reference's procedural sky (CPT.cpp:286-292) */
+  const float* env_rgb;
+  int32_t env_size;
 } twin_params;
 
 typedef struct twin_material {

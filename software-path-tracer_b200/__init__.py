@@ -54,6 +54,13 @@ class Stats(ctypes.Structure):
     ]
 
 
+class PostProcess(ctypes.Structure):
+    _fields_ = [("exposure", ctypes.c_float), ("tonemap", ctypes.c_int32), ("srgb", ctypes.c_int32),
+                ("auto_exposure", ctypes.c_int32), ("target_luminance", ctypes.c_float)]
+
+
+TONEMAP_NONE, TONEMAP_REINHARD, TONEMAP_ACES = 0, 1, 2
+
 MATERIAL_DTYPE = np.dtype([("albedo", np.float32, 3), ("type", np.uint32), ("emission", np.float32, 3),
                            ("param", np.float32)])
 
@@ -67,6 +74,7 @@ EXPORTS = [
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
     "cudapt_set_frame_count",
+    "cudapt_upload_environment", "cudapt_default_postprocess", "cudapt_set_postprocess", "cudapt_get_exposure", "cudapt_write_image",
 ]
 
 _lib = None
@@ -116,6 +124,12 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_stream.argtypes = [vp]
     lib.cudapt_stream.restype = vp
     lib.cudapt_set_frame_count.argtypes = [vp, u32]
+    lib.cudapt_upload_environment.argtypes = [vp, vp, u32]
+    lib.cudapt_default_postprocess.argtypes = [ctypes.POINTER(PostProcess)]
+    lib.cudapt_default_postprocess.restype = None
+    lib.cudapt_set_postprocess.argtypes = [vp, ctypes.POINTER(PostProcess)]
+    lib.cudapt_get_exposure.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    lib.cudapt_write_image.argtypes = [vp, ctypes.c_char_p]
     _lib = lib
     return lib
 
@@ -139,6 +153,16 @@ def default_camera(**kw) -> Camera:
         else:
             setattr(c, k, (ctypes.c_float * 3)(*[float(x) for x in v]))
     return c
+
+
+def default_postprocess(**kw) -> PostProcess:
+    p = PostProcess()
+    load_library().cudapt_default_postprocess(ctypes.byref(p))
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise AttributeError(k)
+        setattr(p, k, v)
+    return p
 
 
 def _p(a):
@@ -215,6 +239,15 @@ class PathTracer:
     def reupload_scene(self):
         self._chk(self._lib.cudapt_reupload_scene(self._h))
 
+    def upload_environment(self, rgb):
+        """Octahedral environment map, (n, n, 3) float32; None restores the procedural sky."""
+        if rgb is None:
+            self._chk(self._lib.cudapt_upload_environment(self._h, None, 0))
+            return
+        e = np.ascontiguousarray(rgb, np.float32)
+        assert e.ndim == 3 and e.shape[0] == e.shape[1] and e.shape[2] == 3
+        self._chk(self._lib.cudapt_upload_environment(self._h, _p(e), e.shape[0]))
+
     # rendering
     def reset(self):
         self._chk(self._lib.cudapt_reset(self._h))
@@ -231,6 +264,17 @@ class PathTracer:
             out = np.empty((self.height, self.width), np.uint32)
         self._chk(self._lib.cudapt_resolve_rgba8(self._h, _p(out)))
         return out
+
+    def set_postprocess(self, post: PostProcess):
+        self._chk(self._lib.cudapt_set_postprocess(self._h, ctypes.byref(post)))
+
+    def exposure(self) -> float:
+        e = ctypes.c_float()
+        self._chk(self._lib.cudapt_get_exposure(self._h, ctypes.byref(e)))
+        return e.value
+
+    def write_image(self, path: str):
+        self._chk(self._lib.cudapt_write_image(self._h, os.fsencode(path)))
 
     def read_accum(self):
         out = np.empty((self.height, self.width, 4), np.float32)

@@ -46,6 +46,16 @@ struct cudapt_ctx {
   uint32_t part_rank = 0, part_world = 1, tile_w = 32, tile_h = 32;
   bool counting = false;
 
+  // environment map (octahedral), or nullptr = procedural sky
+  float4* d_env = nullptr;
+  uint32_t env_size = 0;
+
+  // post-process (resolve stage)
+  cudapt_postprocess post{};
+  float* d_lum_partials = nullptr;  // auto-exposure scratch: partial sums | [n] = exposure
+  uint32_t lum_capacity = 0;
+  float last_exposure = 1.0f;
+
   // stats
   uint64_t launches = 0;
   double render_ms = 0.0, last_render_ms = 0.0, last_trace_ms = 0.0;
@@ -106,7 +116,7 @@ ImageParams image_params(const cudapt_ctx* ctx) {
   return im;
 }
 
-IntegratorParams integrator_params(const cudapt_config& c) {
+IntegratorParams integrator_params(const cudapt_config& c, const float4* env = nullptr, uint32_t env_size = 0) {
   IntegratorParams ip;
   ip.rng_mode = c.rng_mode;
   ip.max_bounces = c.max_bounces;
@@ -118,6 +128,8 @@ IntegratorParams integrator_params(const cudapt_config& c) {
   ip.albedo = c.albedo;
   ip.sky_scale = c.sky_scale;
   ip.seed = c.seed;
+  ip.env = env;
+  ip.env_size = env ? env_size : 0u;
   return ip;
 }
 
@@ -205,6 +217,7 @@ int cudapt_create(const cudapt_config* cfg, cudapt_ctx** out) {
   ctx->cfg = c;
   ctx->sm_count = prop.multiProcessorCount;
   cudapt_default_camera(&ctx->cam);
+  cudapt_default_postprocess(&ctx->post);
   ctx->mesh.sm_count = ctx->sm_count;
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
@@ -229,6 +242,8 @@ void cudapt_destroy(cudapt_ctx* ctx) {
   cudaFree(ctx->d_aov_prim);
   cudaFree(ctx->d_aov_t);
   cudaFree(ctx->d_counters);
+  cudaFree(ctx->d_lum_partials);
+  cudaFree(ctx->d_env);
   if (ctx->h_pinned_rgba) cudaFreeHost(ctx->h_pinned_rgba);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -342,6 +357,25 @@ int cudapt_reupload_scene(cudapt_ctx* ctx) {
   return restart_accumulation(ctx);
 }
 
+int cudapt_upload_environment(cudapt_ctx* ctx, const float* rgb, uint32_t size) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (size > 16384u) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_upload_environment: size %u too large", size);
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(ctx->d_env);
+  ctx->d_env = nullptr;
+  ctx->env_size = 0;
+  if (rgb && size) {
+    const size_t n = (size_t)size * size;
+    std::vector<float4> texels(n);
+    for (size_t i = 0; i < n; ++i) texels[i] = make_float4(rgb[3 * i + 0], rgb[3 * i + 1], rgb[3 * i + 2], 0.0f);
+    CU_TRY(ctx, cudaMalloc(&ctx->d_env, sizeof(float4) * n));
+    CU_TRY(ctx, cudaMemcpy(ctx->d_env, texels.data(), sizeof(float4) * n, cudaMemcpyHostToDevice));
+    ctx->env_size = size;
+  }
+  return restart_accumulation(ctx);
+}
+
 int cudapt_reset(cudapt_ctx* ctx) {
   if (!ctx) return CUDAPT_ERR_INVALID;
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
@@ -378,7 +412,7 @@ int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
     a.frame_stride = ctx->frame_stride;
     a.cam = camera_params(ctx->cam);
     a.im = image_params(ctx);
-    a.ip = integrator_params(ctx->cfg);
+    a.ip = integrator_params(ctx->cfg, ctx->d_env, ctx->env_size);
     CU_TRY(ctx, launch_render_spheres(a, ctx->cfg.rng_mode == CUDAPT_RNG_PHILOX, ctx->stream));
     ctx->launches += 1;
   } else {
@@ -394,7 +428,7 @@ int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
     ra.frame_stride = ctx->frame_stride;
     ra.cam = camera_params(ctx->cam);
     ra.im = image_params(ctx);
-    ra.ip = integrator_params(ctx->cfg);
+    ra.ip = integrator_params(ctx->cfg, ctx->d_env, ctx->env_size);
     ra.samples_per_pass = (uint32_t)ctx->cfg.samples_per_pass;
     ra.counting = ctx->counting;
     std::string err;
@@ -416,18 +450,117 @@ int cudapt_synchronize(cudapt_ctx* ctx) {
   return finish_timing(ctx);
 }
 
-int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
-  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
-  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_resolve_rgba8: resolution not set");
-  if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "cudapt_resolve_rgba8: no frames rendered yet");
+void cudapt_default_postprocess(cudapt_postprocess* pp) {
+  std::memset(pp, 0, sizeof(*pp));
+  pp->exposure = 1.0f;           // Types.h:87
+  pp->tonemap = CUDAPT_TONEMAP_NONE;
+  pp->srgb = 0;
+  pp->auto_exposure = 0;         // Types.h:88
+  pp->target_luminance = 0.18f;  // Types.h:89
+}
+
+int cudapt_set_postprocess(cudapt_ctx* ctx, const cudapt_postprocess* pp) {
+  if (!ctx || !pp) return CUDAPT_ERR_INVALID;
+  if (pp->tonemap < CUDAPT_TONEMAP_NONE || pp->tonemap > CUDAPT_TONEMAP_ACES || !(pp->exposure >= 0.0f) ||
+      !(pp->target_luminance > 0.0f))
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_set_postprocess: invalid parameters");
+  ctx->post = *pp;  // a display setting: the accumulation is NOT restarted
+  return CUDAPT_OK;
+}
+
+int cudapt_get_exposure(cudapt_ctx* ctx, float* exposure) {
+  if (!ctx || !exposure) return CUDAPT_ERR_INVALID;
+  *exposure = ctx->last_exposure;
+  return CUDAPT_OK;
+}
+
+namespace {
+// resolve (+ auto-exposure) into d_rgba and the pinned staging buffer; synchronises the stream
+int resolve_to_pinned(cudapt_ctx* ctx, const char* who) {
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "%s: resolution not set", who);
+  if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "%s: no frames rendered yet", who);
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   const uint32_t n = ctx->width * ctx->height;
-  CU_TRY(ctx, launch_resolve_rgba8(ctx->d_accum, ctx->d_rgba, n, ctx->frame_count, ctx->stream));
-  ctx->launches += 1;
+  const cudapt_postprocess& pp = ctx->post;
+  const bool plain = pp.exposure == 1.0f && pp.tonemap == CUDAPT_TONEMAP_NONE && !pp.srgb && !pp.auto_exposure;
+  const float* d_exposure = nullptr;
+  if (plain) {
+    CU_TRY(ctx, launch_resolve_rgba8(ctx->d_accum, ctx->d_rgba, n, ctx->frame_count, ctx->stream));  // CPT.cpp:87-117 as is
+    ctx->launches += 1;
+  } else {
+    if (pp.auto_exposure) {
+      const uint32_t np = auto_exposure_partials(n);
+      if (ctx->lum_capacity < np + 1) {
+        cudaFree(ctx->d_lum_partials);
+        ctx->d_lum_partials = nullptr;
+        CU_TRY(ctx, cudaMalloc(&ctx->d_lum_partials, sizeof(float) * (size_t)(np + 1)));
+        ctx->lum_capacity = np + 1;
+      }
+      CU_TRY(ctx, launch_auto_exposure(ctx->d_accum, n, ctx->frame_count, pp.target_luminance, ctx->d_lum_partials,
+                                       ctx->d_lum_partials + np, ctx->stream));
+      ctx->launches += 2;
+      d_exposure = ctx->d_lum_partials + np;
+    }
+    CU_TRY(ctx, launch_resolve_post(ctx->d_accum, ctx->d_rgba, n, ctx->frame_count, pp.exposure, d_exposure, pp.tonemap, pp.srgb,
+                                    ctx->stream));
+    ctx->launches += 1;
+  }
   CU_TRY(ctx, cudaMemcpyAsync(ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  ctx->last_exposure = pp.exposure;
+  if (d_exposure) CU_TRY(ctx, cudaMemcpyAsync(&ctx->last_exposure, d_exposure, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * (size_t)n);
   return finish_timing(ctx);
+}
+}  // namespace
+
+int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
+  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  const int rc = resolve_to_pinned(ctx, "cudapt_resolve_rgba8");
+  if (rc != CUDAPT_OK) return rc;
+  std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * (size_t)ctx->width * ctx->height);
+  return CUDAPT_OK;
+}
+
+int cudapt_write_image(cudapt_ctx* ctx, const char* path) {
+  if (!ctx || !path) return CUDAPT_ERR_INVALID;
+  const size_t len = std::strlen(path);
+  const bool ppm = len > 4 && std::strcmp(path + len - 4, ".ppm") == 0;
+  const bool pfm = len > 4 && std::strcmp(path + len - 4, ".pfm") == 0;
+  if (!ppm && !pfm) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: '%s' is neither .ppm nor .pfm", path);
+  const uint32_t W = ctx->width, H = ctx->height;
+  if (ppm) {
+    const int rc = resolve_to_pinned(ctx, "cudapt_write_image");
+    if (rc != CUDAPT_OK) return rc;
+    std::vector<unsigned char> rgb((size_t)W * H * 3);
+    for (size_t i = 0; i < (size_t)W * H; ++i) {
+      const uint32_t p = ctx->h_pinned_rgba[i];  // R<<24 | G<<16 | B<<8 | A (Color.h:9)
+      rgb[3 * i + 0] = (unsigned char)(p >> 24);
+      rgb[3 * i + 1] = (unsigned char)(p >> 16);
+      rgb[3 * i + 2] = (unsigned char)(p >> 8);
+    }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: cannot open '%s'", path);
+    std::fprintf(f, "P6\n%u %u\n255\n", W, H);
+    const bool ok = std::fwrite(rgb.data(), 1, rgb.size(), f) == rgb.size();
+    std::fclose(f);
+    return ok ? CUDAPT_OK : fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: short write to '%s'", path);
+  }
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: resolution not set");
+  if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "cudapt_write_image: no frames rendered yet");
+  std::vector<float> acc((size_t)W * H * 4);
+  uint32_t fc = 0;
+  const int rc = cudapt_read_accum(ctx, acc.data(), &fc);
+  if (rc != CUDAPT_OK) return rc;
+  std::vector<float> rgb((size_t)W * H * 3);
+  for (uint32_t y = 0; y < H; ++y)  // PFM stores the bottom row first
+    for (uint32_t x = 0; x < W; ++x)
+      for (int c = 0; c < 3; ++c) rgb[3 * ((size_t)(H - 1 - y) * W + x) + c] = acc[4 * ((size_t)y * W + x) + c] / (float)fc;
+  FILE* f = std::fopen(path, "wb");
+  if (!f) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: cannot open '%s'", path);
+  std::fprintf(f, "PF\n%u %u\n-1.0\n", W, H);
+  const bool ok = std::fwrite(rgb.data(), sizeof(float), rgb.size(), f) == rgb.size();
+  std::fclose(f);
+  return ok ? CUDAPT_OK : fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: short write to '%s'", path);
 }
 
 int cudapt_read_accum(cudapt_ctx* ctx, float* host_out, uint32_t* frame_count) {

@@ -134,7 +134,36 @@ struct IntegratorParams {
   int32_t rng_mode, max_bounces, rr_start, jitter, nee;
   float tnear, eps, albedo, sky_scale;
   uint32_t seed;
+  const float4* env;  // octahedral environment map (env_size x env_size texels, rgb + pad) or nullptr = procedural sky
+  uint32_t env_size;
 };
+
+// Radiance arriving from direction d when nothing is hit: the reference's procedural sky (CPT.cpp:286-292), or --
+// SURVEY.md 8f-4, after the commented-out Scene::setEnvironmentMap of libs/render/src/Scene.cpp:124-169 -- a
+// bilinear lookup in an OCTAHEDRAL map (pole axis +Y).  The octahedral mapping needs only + - * / and
+// comparisons (no atan2/acos), so the CPU oracle reproduces every texel address and weight bit for bit.
+__device__ __forceinline__ f3 sky_radiance(const IntegratorParams& ip, f3 d) {
+  if (ip.env == nullptr) return sample_sky(d);
+  const float s = (fabsf(d.x) + fabsf(d.y)) + fabsf(d.z);
+  float px = d.x / s, pz = d.z / s;
+  if (d.y < 0.0f) {  // lower hemisphere: fold the corners outwards
+    const float fx = 1.0f - fabsf(pz), fz = 1.0f - fabsf(px);
+    px = d.x < 0.0f ? -fx : fx;
+    pz = d.z < 0.0f ? -fz : fz;
+  }
+  const float n = (float)ip.env_size, hi = (float)(ip.env_size - 1u);
+  float x = (px * 0.5f + 0.5f) * n - 0.5f, y = (pz * 0.5f + 0.5f) * n - 0.5f;
+  x = x < 0.0f ? 0.0f : (x > hi ? hi : x);
+  y = y < 0.0f ? 0.0f : (y > hi ? hi : y);
+  const uint32_t x0 = (uint32_t)x, y0 = (uint32_t)y;
+  const uint32_t x1 = x0 + 1u < ip.env_size ? x0 + 1u : x0, y1 = y0 + 1u < ip.env_size ? y0 + 1u : y0;
+  const float fx = x - (float)x0, fy = y - (float)y0, gx = 1.0f - fx, gy = 1.0f - fy;
+  const float4 c00 = __ldg(ip.env + (size_t)y0 * ip.env_size + x0), c10 = __ldg(ip.env + (size_t)y0 * ip.env_size + x1);
+  const float4 c01 = __ldg(ip.env + (size_t)y1 * ip.env_size + x0), c11 = __ldg(ip.env + (size_t)y1 * ip.env_size + x1);
+  return mk3((c00.x * gx + c10.x * fx) * gy + (c01.x * gx + c11.x * fx) * fy,
+             (c00.y * gx + c10.y * fx) * gy + (c01.y * gx + c11.y * fx) * fy,
+             (c00.z * gx + c10.z * fx) * gy + (c01.z * gx + c11.z * fx) * fy);
+}
 
 __device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) {
   // values are small per thread; sum in 32 bit across the warp

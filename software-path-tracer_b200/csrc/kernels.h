@@ -33,7 +33,12 @@ struct SphereLaunch {
 cudaError_t launch_render_spheres(const SphereLaunch& a, bool philox, cudaStream_t stream);
 cudaError_t launch_resolve_rgba8(const float4* accum, uint32_t* out, uint32_t n_pixels, uint32_t frame_count,
                                  cudaStream_t stream);
-
+// post.cu: resolve + exposure / tone map / sRGB, and the auto-exposure reduction
+uint32_t auto_exposure_partials(uint32_t n_pixels);
+cudaError_t launch_auto_exposure(const float4* accum, uint32_t n_pixels, uint32_t frame_count, float target, float* partials,
+                                 float* exposure_out, cudaStream_t stream);
+cudaError_t launch_resolve_post(const float4* accum, uint32_t* out, uint32_t n_pixels, uint32_t frame_count, float exposure,
+                                const float* exposure_ptr, int tonemap, int srgb, cudaStream_t stream);
 
 // ---- mesh wavefront integrator (wavefront.cu, trace_bvh.cu) -------------------------------------------
 // Path state lives in HBM as structure-of-arrays indexed by PATH ID = sample_in_pass * n_pixels + pixel;

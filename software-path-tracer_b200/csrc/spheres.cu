@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(kSphereBlockX* kSphereBlockY)
         a.aov_t[pixel] = h.t;
       }
       if (h.idx < 0) {  // CPT.cpp:231-235
-        const f3 sky = sample_sky(d);
+        const f3 sky = sky_radiance(a.ip, d);
         L = L + thr * (a.ip.sky_scale == 1.0f ? sky : sky * a.ip.sky_scale);
         done = true;
       } else {

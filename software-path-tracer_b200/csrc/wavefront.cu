@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
         p.aov_t[pixel] = t;
       }
       if (h.y == 0xFFFFFFFFu) {  // miss: CPT.cpp:231-235
-        const f3 sky = sample_sky(d);
+        const f3 sky = sky_radiance(p.ip, d);
         L = L + thr * (sky * p.ip.sky_scale);
         L_dirty = true;
         ++n_paths;

@@ -260,3 +260,27 @@ def rock_field(n_instances=200_000, seed=0xC4, extent_x=(-50.0, 50.0), extent_z=
         material((0.35, 0.4, 0.6), GGX_COATED, param=0.4),
     ], MATERIAL_DTYPE)
     return v, t, mid, mats
+
+
+def octahedral_environment(size=64, sun_dir=(0.4, 0.7, 0.6), sun_power=40.0, seed=0xE0):
+    """Synthetic HDR environment as a size x size octahedral map (pole +Y, layout of cudapt_upload_environment):
+    the reference's sky gradient (CPT.cpp:286-292) plus a bright sun lobe and a little hashed texture, so that a
+    wrong texel address or weight shows up in parity tests."""
+    j, i = np.meshgrid(np.arange(size), np.arange(size), indexing="ij")
+    u = (i + 0.5) / size * 2.0 - 1.0  # p.x
+    v = (j + 0.5) / size * 2.0 - 1.0  # p.z
+    y = 1.0 - np.abs(u) - np.abs(v)
+    x, z = u.copy(), v.copy()
+    lower = y < 0
+    x[lower] = (1.0 - np.abs(v[lower])) * np.where(u[lower] < 0, -1.0, 1.0)
+    z[lower] = (1.0 - np.abs(u[lower])) * np.where(v[lower] < 0, -1.0, 1.0)
+    d = np.stack([x, y, z], -1)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    t = 0.5 * (d[..., 1] + 1.0)
+    sky = (1.0 - t)[..., None] * np.array([1.0, 1.0, 1.0]) + t[..., None] * np.array([0.5, 0.7, 1.0])
+    s = np.asarray(sun_dir, np.float64)
+    s /= np.linalg.norm(s)
+    lobe = np.clip(d @ s, 0.0, 1.0) ** 64
+    sun = sun_power * lobe[..., None] * np.array([1.0, 0.9, 0.7])
+    grain = 0.1 * _hash01(i.astype(np.uint32), j.astype(np.uint32), np.uint32(seed))[..., None]
+    return np.ascontiguousarray(sky + sun + grain, np.float32)

@@ -185,3 +185,17 @@ def test_twin_mesh_cornell_energy(oracle, scenes):
     ma, mb = a[..., :3].mean() / N, b[..., :3].mean() / (N * 4)
     assert ma > 0.02
     assert abs(ma - mb) / mb < 0.12
+
+
+def test_post_resolve_defaults_equal_reference_resolve(oracle):
+    """The numpy restatement of the resolve/post-process stage degenerates to the reference's resolve
+    (CPT.cpp:87-117, here through the twin, which is pinned bit-for-bit to the reference TUs above)."""
+    rng = np.random.default_rng(7)
+    acc = (rng.random((37, 53, 4), dtype=np.float32) * 9.0).astype(np.float32)
+    acc[..., 3] = 6.0
+    acc[0, 0, :3] = [-1.0, 0.0, 1e9]
+    assert np.array_equal(oracle.post_resolve_rgba8(acc, 6)[0], oracle.twin_resolve_rgba8(acc, 6))
+    # Reinhard and ACES known answers at c = 1: 1/2 -> 127, (2.54)/(3.16) -> (uint8)(0.8037975 * 255) = 204
+    one = np.full((1, 1, 4), 1.0, np.float32)
+    assert (oracle.post_resolve_rgba8(one, 1, tonemap=1)[0][0, 0] >> 24) == 127
+    assert (oracle.post_resolve_rgba8(one, 1, tonemap=2)[0][0, 0] >> 24) == 204
