@@ -194,6 +194,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
+    ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],
+                    help="N > 1 read-back tail: 'fused' = one reduce-scatter+resolve+gather kernel per rank over NVLink "
+                         "peer memory (cudapt_reduce_resolve_peers); 'nccl' = NCCL reduce of the float buffer to rank 0")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -247,12 +250,33 @@ def main():
         accum_t = torch.as_tensor(_Cai(), device=f"cuda:{local_rank}")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
 
+    # fused tail: exchange CUDA IPC handles once, map every peer's accumulation buffer and the root's outputs
+    fused = world > 1 and args.tail == "fused"
+    peer_accum, root_rgba, root_accum, tick = None, None, None, None
+    if fused:
+        handles = [None] * world
+        dist.all_gather_object(handles, tr.ipc_export())
+        peer_accum = [tr.accum_device_ptr if g == rank else tr.ipc_open(handles[g][0]) for g in range(world)]
+        root_rgba = tr.rgba_device_ptr if rank == 0 else tr.ipc_open(handles[0][1])
+        root_accum = peer_accum[0]
+        tick = torch.zeros(1, dtype=torch.int32, device=f"cuda:{local_rank}")
+
+    def tail():
+        """Read-back boundary of a step, enqueued on libcudapt's stream (no host synchronisation)."""
+        if world == 1:
+            return
+        with torch.cuda.stream(stream):
+            if fused:
+                dist.all_reduce(tick)   # stream-ordered rendezvous: every rank's render is complete
+                tr.reduce_resolve_peers(peer_accum, rank, spp * world, root_rgba, root_accum)
+                dist.all_reduce(tick)   # every rank's slice has landed in the root's buffers
+            else:
+                part.reduce_accum(accum_t, dst=0)
+
     def step():
         tr.reset()
         tr.render(spp)
-        if world > 1:
-            with torch.cuda.stream(stream):
-                part.reduce_accum(accum_t, dst=0)
+        tail()
 
     def sync_all():
         tr.synchronize()
@@ -308,11 +332,16 @@ def main():
         else:
             tr.reupload_scene()
         tr.render(spp)
+        tail()
         if world > 1:
-            with torch.cuda.stream(stream):
-                part.reduce_accum(accum_t, dst=0)
             tr.set_frame_count(spp * world if rank == 0 else spp)
-        tr.resolve_rgba8(host_rgba)                  # resolve kernel + D2H + sync
+        if fused:
+            if rank == 0:
+                host_rgba[...] = tr.download_rgba8()   # the image the ranks assembled in the root's buffer: D2H + sync
+            else:
+                tr.synchronize()
+        else:
+            tr.resolve_rgba8(host_rgba)              # resolve kernel + D2H + sync
 
     e2e_step()
     sync_all()
@@ -338,8 +367,11 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "name": wl["name"], "width": W, "height": H, "spp_per_gpu": spp,
                    "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
-                   "partition": "one process per GPU; sample ranges per rank; NCCL reduce(sum) of the float "
-                                "accumulation buffer to rank 0 at the end of every step" if world > 1 else "single GPU"},
+                   "partition": ("one process per GPU; sample ranges per rank; " +
+                                 ("fused tail every step: one reduce-scatter + resolve + gather kernel per rank over "
+                                  "NVLink peer memory (CUDA IPC), rank-ordered sums" if fused else
+                                  "NCCL reduce(sum) of the float accumulation buffer to rank 0 at the end of every step"))
+                   if world > 1 else "single GPU"},
         "mrays_per_s": value * rays_per_path, "rays_per_path": rays_per_path,
         "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(scene_bytes),
                 "d2h_bytes_per_step": int(n_px * 4)},

@@ -134,6 +134,15 @@ int cudapt_build_accel(cudapt_ctx* ctx);
  * changed on the host without changing topology (the reference re-commits its Embree scene whenever
  * Scene::hasChanges(), CPT.cpp:122-131,156-160). */
 int cudapt_reupload_scene(cudapt_ctx* ctx);
+/* Incremental scene update: the triangle mesh keeps its indices and materials, the nv vertices
+ * (same count as uploaded) move.  The BVH is REFIT on the host -- tree, child slots and triangle order are kept,
+ * every box and quantisation grid is recomputed bottom-up -- and uploaded again; accumulation restarts.  This is
+ * what the reference's dirty-bit handshake (Scene::hasChanges()/markChangesProcessed(), Scene.h:207-215,
+ * CPT.cpp:122-131,156-160) would trigger if anything ever set the bit again (nothing does), and
+ * it fixes the reference's rebuild bug (geometries are never detached, CPT.cpp:362-403): update = replace.
+ * Because the closest-hit rule does not depend on the acceleration structure, the image after an update is
+ * bit-identical to a fresh build of the moved mesh. */
+int cudapt_update_vertices(cudapt_ctx* ctx, const float* vertices, uint32_t nv);
 
 /* Environment map replacing the procedural sky on a miss (reference anchor: the commented-out
  * Scene::setEnvironmentMap, libs/render/src/Scene.cpp:124-169, and the SkyBox of Scene.h:268-278).  rgb is a
@@ -203,6 +212,27 @@ void* cudapt_accum_device_ptr(cudapt_ctx* ctx);  /* float4[W*H] */
 void* cudapt_stream(cudapt_ctx* ctx);            /* cudaStream_t all work is enqueued on */
 /* Declare that the accumulation buffer now holds frame_count samples per pixel (after an external reduce). */
 int cudapt_set_frame_count(cudapt_ctx* ctx, uint32_t frame_count);
+
+/* ---- fused multi-GPU read-back tail over NVLink peer memory (SURVEY.md 8e "fusion opportunity") ---------- */
+/* One kernel per rank does reduce-scatter + resolve + gather: rank r owns pixels [n*r/G, n*(r+1)/G); it loads
+ * the float4 accumulation of EVERY rank for those pixels (accum_by_rank[g], g = 0..G-1 in rank order, each a
+ * device pointer valid on this context's device: its own buffer, another context's, or a peer mapping obtained
+ * with cudapt_ipc_open), adds them in rank order, applies the post-process stage with total_frames and stores
+ * the RGBA8 words into root_rgba and -- unless NULL -- the float4 sums into root_accum (both may be peer
+ * mappings of the root's buffers; root_accum may alias accum_by_rank[root]).  Auto-exposure is not available
+ * here (it needs the whole image).  The caller orders the ranks: every rank's render must have completed before
+ * any rank launches this (e.g. a barrier on the streams), and the root reads its buffers after all ranks did. */
+int cudapt_reduce_resolve_peers(cudapt_ctx* ctx, const void* const* accum_by_rank, uint32_t n_ranks, uint32_t rank,
+                                uint32_t total_frames, void* root_rgba, void* root_accum);
+void* cudapt_rgba_device_ptr(cudapt_ctx* ctx);  /* uint32[W*H], the buffer cudapt_resolve_rgba8 fills */
+/* Copies the context's RGBA8 device buffer to the host as it is (after peers wrote their slices). */
+int cudapt_download_rgba8(cudapt_ctx* ctx, uint32_t* host_out);
+/* CUDA IPC plumbing for one-process-per-GPU launches: 64-byte handles of the accumulation and RGBA8 buffers
+ * (valid until the next cudapt_set_resolution), and mapping/unmapping of a peer's handle on this device. */
+#define CUDAPT_IPC_HANDLE_BYTES 64
+int cudapt_ipc_export(cudapt_ctx* ctx, void* accum_handle, void* rgba_handle);
+int cudapt_ipc_open(cudapt_ctx* ctx, const void* handle, void** device_ptr);
+int cudapt_ipc_close(cudapt_ctx* ctx, void* device_ptr);
 
 #ifdef __cplusplus
 }

@@ -69,11 +69,13 @@ EXPORTS = [
     "cudapt_default_config", "cudapt_default_camera", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
-    "cudapt_reupload_scene",
+    "cudapt_reupload_scene", "cudapt_update_vertices",
     "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
     "cudapt_set_frame_count",
+    "cudapt_reduce_resolve_peers", "cudapt_rgba_device_ptr", "cudapt_download_rgba8", "cudapt_ipc_export",
+    "cudapt_ipc_open", "cudapt_ipc_close",
     "cudapt_upload_environment", "cudapt_default_postprocess", "cudapt_set_postprocess", "cudapt_get_exposure", "cudapt_write_image",
 ]
 
@@ -108,6 +110,7 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_upload_materials.argtypes = [vp, vp, u32]
     lib.cudapt_build_accel.argtypes = [vp]
     lib.cudapt_reupload_scene.argtypes = [vp]
+    lib.cudapt_update_vertices.argtypes = [vp, vp, u32]
     lib.cudapt_reset.argtypes = [vp]
     lib.cudapt_render.argtypes = [vp, u32]
     lib.cudapt_synchronize.argtypes = [vp]
@@ -125,6 +128,13 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_stream.restype = vp
     lib.cudapt_set_frame_count.argtypes = [vp, u32]
     lib.cudapt_upload_environment.argtypes = [vp, vp, u32]
+    lib.cudapt_reduce_resolve_peers.argtypes = [vp, ctypes.POINTER(vp), u32, u32, u32, vp, vp]
+    lib.cudapt_rgba_device_ptr.argtypes = [vp]
+    lib.cudapt_rgba_device_ptr.restype = vp
+    lib.cudapt_download_rgba8.argtypes = [vp, vp]
+    lib.cudapt_ipc_export.argtypes = [vp, vp, vp]
+    lib.cudapt_ipc_open.argtypes = [vp, vp, ctypes.POINTER(vp)]
+    lib.cudapt_ipc_close.argtypes = [vp, vp]
     lib.cudapt_default_postprocess.argtypes = [ctypes.POINTER(PostProcess)]
     lib.cudapt_default_postprocess.restype = None
     lib.cudapt_set_postprocess.argtypes = [vp, ctypes.POINTER(PostProcess)]
@@ -236,6 +246,10 @@ class PathTracer:
     def build_accel(self):
         self._chk(self._lib.cudapt_build_accel(self._h))
 
+    def update_vertices(self, vertices):
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        self._chk(self._lib.cudapt_update_vertices(self._h, _p(v), len(v)))
+
     def reupload_scene(self):
         self._chk(self._lib.cudapt_reupload_scene(self._h))
 
@@ -310,6 +324,35 @@ class PathTracer:
 
     def set_frame_count(self, n: int):
         self._chk(self._lib.cudapt_set_frame_count(self._h, n))
+
+    # fused multi-GPU read-back tail
+    def reduce_resolve_peers(self, accum_by_rank, rank: int, total_frames: int, root_rgba: int, root_accum: int | None = None):
+        arr = (ctypes.c_void_p * len(accum_by_rank))(*[ctypes.c_void_p(int(a)) for a in accum_by_rank])
+        self._chk(self._lib.cudapt_reduce_resolve_peers(self._h, arr, len(accum_by_rank), rank, total_frames,
+                                                        ctypes.c_void_p(int(root_rgba)),
+                                                        ctypes.c_void_p(int(root_accum)) if root_accum else None))
+
+    def download_rgba8(self) -> np.ndarray:
+        out = np.empty((self.height, self.width), np.uint32)
+        self._chk(self._lib.cudapt_download_rgba8(self._h, _p(out)))
+        return out
+
+    def ipc_export(self):
+        a, r = ctypes.create_string_buffer(64), ctypes.create_string_buffer(64)
+        self._chk(self._lib.cudapt_ipc_export(self._h, a, r))
+        return a.raw, r.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        p = ctypes.c_void_p()
+        self._chk(self._lib.cudapt_ipc_open(self._h, ctypes.c_char_p(handle), ctypes.byref(p)))
+        return int(p.value)
+
+    def ipc_close(self, ptr: int):
+        self._chk(self._lib.cudapt_ipc_close(self._h, ctypes.c_void_p(int(ptr))))
+
+    @property
+    def rgba_device_ptr(self) -> int:
+        return int(self._lib.cudapt_rgba_device_ptr(self._h) or 0)
 
     @property
     def accum_device_ptr(self) -> int:

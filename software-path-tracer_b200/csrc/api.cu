@@ -357,6 +357,16 @@ int cudapt_reupload_scene(cudapt_ctx* ctx) {
   return restart_accumulation(ctx);
 }
 
+int cudapt_update_vertices(cudapt_ctx* ctx, const float* vertices, uint32_t nv) {
+  if (!ctx || !vertices) return CUDAPT_ERR_INVALID;
+  if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_update_vertices: no built mesh scene");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // the pinned staging buffer may still be in flight
+  std::string err;
+  if (!ctx->mesh.update_vertices(vertices, nv, ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_update_vertices: %s", err.c_str());
+  return restart_accumulation(ctx);
+}
+
 int cudapt_upload_environment(cudapt_ctx* ctx, const float* rgb, uint32_t size) {
   if (!ctx) return CUDAPT_ERR_INVALID;
   if (size > 16384u) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_upload_environment: size %u too large", size);
@@ -661,3 +671,61 @@ int cudapt_set_frame_count(cudapt_ctx* ctx, uint32_t frame_count) {
 }
 
 }  // extern "C"
+
+// ---- fused multi-GPU read-back tail ------------------------------------------------------------------------
+int cudapt_reduce_resolve_peers(cudapt_ctx* ctx, const void* const* accum_by_rank, uint32_t n_ranks, uint32_t rank,
+                                uint32_t total_frames, void* root_rgba, void* root_accum) {
+  if (!ctx || !accum_by_rank || !root_rgba) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_reduce_resolve_peers: resolution not set");
+  if (n_ranks < 1 || n_ranks > 16 || rank >= n_ranks) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_reduce_resolve_peers: rank %u of %u", rank, n_ranks);
+  if (total_frames == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "cudapt_reduce_resolve_peers: no frames");
+  if (ctx->post.auto_exposure) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_reduce_resolve_peers: auto-exposure needs the whole image; resolve on the root instead");
+  for (uint32_t g = 0; g < n_ranks; ++g)
+    if (!accum_by_rank[g]) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_reduce_resolve_peers: accum_by_rank[%u] is NULL", g);
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const uint64_t n = (uint64_t)ctx->width * ctx->height;
+  const uint32_t begin = (uint32_t)(n * rank / n_ranks), end = (uint32_t)(n * (rank + 1) / n_ranks);
+  CU_TRY(ctx, launch_reduce_resolve_peers(reinterpret_cast<const float4* const*>(accum_by_rank), (int)n_ranks, begin, end, total_frames,
+                                          ctx->post.exposure, ctx->post.tonemap, ctx->post.srgb, static_cast<uint32_t*>(root_rgba),
+                                          static_cast<float4*>(root_accum), ctx->sm_count, ctx->stream));
+  ctx->launches += 1;
+  return CUDAPT_OK;
+}
+
+void* cudapt_rgba_device_ptr(cudapt_ctx* ctx) { return ctx ? ctx->d_rgba : nullptr; }
+
+int cudapt_download_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
+  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_rgba) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_download_rgba8: resolution not set");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const size_t n = (size_t)ctx->width * ctx->height;
+  CU_TRY(ctx, cudaMemcpyAsync(ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * n);
+  return finish_timing(ctx);
+}
+
+static_assert(sizeof(cudaIpcMemHandle_t) == CUDAPT_IPC_HANDLE_BYTES, "IPC handle size");
+int cudapt_ipc_export(cudapt_ctx* ctx, void* accum_handle, void* rgba_handle) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_ipc_export: resolution not set");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  if (accum_handle) CU_TRY(ctx, cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(accum_handle), ctx->d_accum));
+  if (rgba_handle) CU_TRY(ctx, cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(rgba_handle), ctx->d_rgba));
+  return CUDAPT_OK;
+}
+int cudapt_ipc_open(cudapt_ctx* ctx, const void* handle, void** device_ptr) {
+  if (!ctx || !handle || !device_ptr) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof(h));
+  CU_TRY(ctx, cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return CUDAPT_OK;
+}
+int cudapt_ipc_close(cudapt_ctx* ctx, void* device_ptr) {
+  if (!ctx || !device_ptr) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CU_TRY(ctx, cudaIpcCloseMemHandle(device_ptr));
+  return CUDAPT_OK;
+}

@@ -67,4 +67,7 @@ constexpr uint32_t kBvh8MaxDepth = 40;  // traversal stack capacity (8 shared + 
 bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, const uint32_t* material_id,
                 int threads, Bvh8* out, std::string* err);
 
+// Incremental update: same indices, moved vertices.  Keeps the tree, refits all boxes.
+bool refit_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, Bvh8* bvh, std::string* err);
+
 }  // namespace cudapt

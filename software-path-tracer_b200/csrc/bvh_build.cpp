@@ -151,6 +151,76 @@ struct Child {
   bool leaf;
 };
 
+// Step 4 of the build, shared with refit_bvh8(): per-axis power-of-two grid anchored at the node box minimum and
+// outward-rounded 8-bit child bounds (exact arithmetic in double, so p + q * 2^e always encloses the child box).
+void quantise_node(const Box& nb, const Box* slot_box, const bool* slot_used, Bvh8Node* Np) {
+  Bvh8Node& N = *Np;
+  int ex[3];
+  for (int k = 0; k < 3; ++k) {
+    N.p[k] = nb.lo[k];
+    const double ext = (double)nb.hi[k] - (double)nb.lo[k];
+    int e = -60;
+    if (ext > 0.0) {
+      int kk;
+      (void)std::frexp(ext / 255.0, &kk);
+      e = kk;
+    }
+    ex[k] = std::min(std::max(e, -125), 126);
+  }
+  uint8_t* qlo[3] = {N.qlo_x, N.qlo_y, N.qlo_z};
+  uint8_t* qhi[3] = {N.qhi_x, N.qhi_y, N.qhi_z};
+  for (int k = 0; k < 3; ++k) {
+    for (;;) {
+      const double scale = std::ldexp(1.0, ex[k]);
+      bool ok = true;
+      for (int s = 0; s < 8 && ok; ++s) {
+        if (!slot_used[s]) {
+          qlo[k][s] = 255;  // empty slot: inverted box, never hit
+          qhi[k][s] = 0;
+          continue;
+        }
+        double l = std::floor(((double)slot_box[s].lo[k] - (double)N.p[k]) / scale);
+        double h = std::ceil(((double)slot_box[s].hi[k] - (double)N.p[k]) / scale);
+        while ((double)N.p[k] + l * scale > (double)slot_box[s].lo[k]) l -= 1.0;
+        while ((double)N.p[k] + h * scale < (double)slot_box[s].hi[k]) h += 1.0;
+        l = std::max(l, 0.0);
+        if (h > 255.0) {
+          ok = false;
+          break;
+        }
+        qlo[k][s] = (uint8_t)l;
+        qhi[k][s] = (uint8_t)std::max(h, 0.0);
+      }
+      if (ok) break;
+      ++ex[k];
+    }
+    N.e[k] = (uint8_t)(ex[k] + 127);
+  }
+}
+
+// Packed record + padded box of one triangle (what the kernels intersect, see build_bvh8()).
+void pack_triangle(const float* vertices, const uint32_t* indices, uint32_t i, uint32_t material, PackedTri* T, float* lo3,
+                   float* hi3) {
+  const float* a = vertices + 3 * (size_t)indices[3 * (size_t)i + 0];
+  const float* b = vertices + 3 * (size_t)indices[3 * (size_t)i + 1];
+  const float* c = vertices + 3 * (size_t)indices[3 * (size_t)i + 2];
+  for (int k = 0; k < 3; ++k) {
+    T->v0[k] = a[k];
+    T->e1[k] = b[k] - a[k];  // single rounding; the kernels (and the CPU oracle) intersect (v0, e1, e2)
+    T->e2[k] = c[k] - a[k];
+    // box of the triangle the kernels actually see: v0, v0+e1, v0+e2 (+ the caller's vertices), padded
+    const float b2 = a[k] + T->e1[k], c2 = a[k] + T->e2[k];
+    float lo = std::min(std::min(a[k], b[k]), std::min(c[k], std::min(b2, c2)));
+    float hi = std::max(std::max(a[k], b[k]), std::max(c[k], std::max(b2, c2)));
+    const float pad = 4e-7f * std::max(std::fabs(lo), std::fabs(hi)) + 1e-30f;
+    lo3[k] = lo - pad;
+    hi3[k] = hi + pad;
+  }
+  T->prim = i;
+  T->material = material;
+  T->pad = 0;
+}
+
 }  // namespace
 
 bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, const uint32_t* material_id,
@@ -164,28 +234,8 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
   std::vector<PackedTri> tri(nt);
   std::vector<float> blo(3 * (size_t)nt), bhi(3 * (size_t)nt), cen(3 * (size_t)nt);
   for (uint32_t i = 0; i < nt; ++i) {
-    const float* a = vertices + 3 * (size_t)indices[3 * (size_t)i + 0];
-    const float* b = vertices + 3 * (size_t)indices[3 * (size_t)i + 1];
-    const float* c = vertices + 3 * (size_t)indices[3 * (size_t)i + 2];
-    PackedTri& T = tri[i];
-    for (int k = 0; k < 3; ++k) {
-      T.v0[k] = a[k];
-      T.e1[k] = b[k] - a[k];  // single rounding; the kernels (and the CPU oracle) intersect (v0, e1, e2)
-      T.e2[k] = c[k] - a[k];
-      // box of the triangle the kernels actually see: v0, v0+e1, v0+e2 (+ the caller's vertices), padded
-      const float b2 = a[k] + T.e1[k], c2 = a[k] + T.e2[k];
-      float lo = std::min(std::min(a[k], b[k]), std::min(c[k], std::min(b2, c2)));
-      float hi = std::max(std::max(a[k], b[k]), std::max(c[k], std::max(b2, c2)));
-      const float pad = 4e-7f * std::max(std::fabs(lo), std::fabs(hi)) + 1e-30f;
-      lo -= pad;
-      hi += pad;
-      blo[3 * (size_t)i + k] = lo;
-      bhi[3 * (size_t)i + k] = hi;
-      cen[3 * (size_t)i + k] = 0.5f * lo + 0.5f * hi;
-    }
-    T.prim = i;
-    T.material = material_id ? material_id[i] : 0u;
-    T.pad = 0;
+    pack_triangle(vertices, indices, i, material_id ? material_id[i] : 0u, &tri[i], &blo[3 * (size_t)i], &bhi[3 * (size_t)i]);
+    for (int k = 0; k < 3; ++k) cen[3 * (size_t)i + k] = 0.5f * blo[3 * (size_t)i + k] + 0.5f * bhi[3 * (size_t)i + k];
   }
   // ---- 1. binary SAH BVH -------------------------------------------------------------------------------
   Builder B;
@@ -274,47 +324,14 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     // 4. quantisation grid
     Bvh8Node N;
     std::memset(&N, 0, sizeof(N));
-    int ex[3];
-    for (int k = 0; k < 3; ++k) {
-      N.p[k] = nb.lo[k];
-      const double ext = (double)nb.hi[k] - (double)nb.lo[k];
-      int e = -60;
-      if (ext > 0.0) {
-        int kk;
-        (void)std::frexp(ext / 255.0, &kk);
-        e = kk;
+    {
+      Box slot_box[8];
+      bool slot_used[8];
+      for (int s8 = 0; s8 < 8; ++s8) {
+        slot_used[s8] = child_in_slot[s8] >= 0;
+        if (slot_used[s8]) slot_box[s8] = ch[child_in_slot[s8]].box;
       }
-      ex[k] = std::min(std::max(e, -125), 126);
-    }
-    uint8_t* qlo[3] = {N.qlo_x, N.qlo_y, N.qlo_z};
-    uint8_t* qhi[3] = {N.qhi_x, N.qhi_y, N.qhi_z};
-    for (int k = 0; k < 3; ++k) {
-      for (;;) {
-        const double scale = std::ldexp(1.0, ex[k]);
-        bool ok = true;
-        for (int s = 0; s < 8 && ok; ++s) {
-          const int i = child_in_slot[s];
-          if (i < 0) {
-            qlo[k][s] = 255;  // empty slot: inverted box, never hit
-            qhi[k][s] = 0;
-            continue;
-          }
-          double l = std::floor(((double)ch[i].box.lo[k] - (double)N.p[k]) / scale);
-          double h = std::ceil(((double)ch[i].box.hi[k] - (double)N.p[k]) / scale);
-          while ((double)N.p[k] + l * scale > (double)ch[i].box.lo[k]) l -= 1.0;
-          while ((double)N.p[k] + h * scale < (double)ch[i].box.hi[k]) h += 1.0;
-          l = std::max(l, 0.0);
-          if (h > 255.0) {
-            ok = false;
-            break;
-          }
-          qlo[k][s] = (uint8_t)l;
-          qhi[k][s] = (uint8_t)std::max(h, 0.0);
-        }
-        if (ok) break;
-        ++ex[k];
-      }
-      N.e[k] = (uint8_t)(ex[k] + 127);
+      quantise_node(nb, slot_box, slot_used, &N);
     }
 
     // 5. emit children in slot order
@@ -355,6 +372,55 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     *err = "internal error: triangle count mismatch after collapse";
     return false;
   }
+  return true;
+}
+
+// Refit after a vertex update (same topology): recomputes the packed triangles and, bottom-up, every node's child
+// boxes and quantisation grid; tree structure, slot assignment and triangle order are kept.  Nodes were emitted
+// breadth-first, so every child has a larger index than its parent and one reverse sweep suffices.
+bool refit_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, Bvh8* bvh, std::string* err) {
+  (void)nv;
+  if (bvh->tris.size() != nt || bvh->nodes.empty()) {
+    *err = "refit: triangle count differs from the built scene";
+    return false;
+  }
+  std::vector<Box> tri_box(nt);  // by leaf-order index
+  for (uint32_t k = 0; k < nt; ++k) {
+    PackedTri& T = bvh->tris[k];
+    const uint32_t prim = T.prim, mat = T.material;
+    if (prim >= nt) {
+      *err = "refit: corrupt triangle record";
+      return false;
+    }
+    pack_triangle(vertices, indices, prim, mat, &T, tri_box[k].lo, tri_box[k].hi);
+  }
+  const size_t nn = bvh->nodes.size();
+  std::vector<Box> node_box(nn);
+  for (size_t i = nn; i-- > 0;) {
+    Bvh8Node& N = bvh->nodes[i];
+    Box slot_box[8], nb;
+    bool slot_used[8];
+    for (int s = 0; s < 8; ++s) {
+      slot_used[s] = false;
+      if (N.imask & (1u << s)) {
+        const uint32_t child = N.child_base + (uint32_t)__builtin_popcount(N.imask & ((1u << s) - 1u));
+        slot_box[s] = node_box[child];
+        slot_used[s] = true;
+      } else {
+        for (uint32_t j = 0; j < 3; ++j) {
+          const uint32_t bit = 8 * j + (uint32_t)s;
+          if (!(N.tri_valid & (1u << bit))) continue;
+          const uint32_t t = N.tri_base + (uint32_t)__builtin_popcount(N.tri_valid & ((1u << bit) - 1u));
+          slot_box[s].grow(tri_box[t]);
+          slot_used[s] = true;
+        }
+      }
+      if (slot_used[s]) nb.grow(slot_box[s]);
+    }
+    quantise_node(nb, slot_box, slot_used, &N);
+    node_box[i] = nb;
+  }
+  for (int k = 0; k < 3; ++k) bvh->world_lo[k] = node_box[0].lo[k], bvh->world_hi[k] = node_box[0].hi[k];
   return true;
 }
 

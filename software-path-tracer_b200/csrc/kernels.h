@@ -40,6 +40,11 @@ cudaError_t launch_auto_exposure(const float4* accum, uint32_t n_pixels, uint32_
 cudaError_t launch_resolve_post(const float4* accum, uint32_t* out, uint32_t n_pixels, uint32_t frame_count, float exposure,
                                 const float* exposure_ptr, int tonemap, int srgb, cudaStream_t stream);
 
+// fused multi-GPU tail: sum over ranks (peer loads, rank order) + post-process + RGBA8 store into the root's buffers
+cudaError_t launch_reduce_resolve_peers(const float4* const* accum_by_rank, int n_ranks, uint32_t begin, uint32_t end,
+                                        uint32_t total_frames, float exposure, int tonemap, int srgb, uint32_t* root_rgba,
+                                        float4* root_accum, int sm_count, cudaStream_t stream);
+
 // ---- mesh wavefront integrator (wavefront.cu, trace_bvh.cu) -------------------------------------------
 // Path state lives in HBM as structure-of-arrays indexed by PATH ID = sample_in_pass * n_pixels + pixel;
 // queues hold 4-byte path ids, so compaction moves indices only.

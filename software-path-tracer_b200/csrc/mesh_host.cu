@@ -138,6 +138,27 @@ bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
   return true;
 }
 
+bool MeshScene::update_vertices(const float* v, uint32_t nv, cudaStream_t stream, std::string* err) {
+  if (!dev_ || !dev_->h_pinned) {
+    *err = "no built scene";
+    return false;
+  }
+  if ((size_t)nv * 3 != vertices_.size()) {
+    *err = "vertex count differs from the uploaded mesh (topology changes need cudapt_upload_mesh + cudapt_build_accel)";
+    return false;
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  vertices_.assign(v, v + 3 * (size_t)nv);
+  Bvh8& bvh = dev_->bvh;
+  if (!refit_bvh8(vertices_.data(), nv, indices_.data(), (uint32_t)(indices_.size() / 3), &bvh, err)) return false;
+  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
+  std::memcpy(dev_->h_pinned, bvh.nodes.data(), nb);
+  std::memcpy((char*)dev_->h_pinned + nb, bvh.tris.data(), tb);
+  refit_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  build_ms = refit_ms;  // reported as accel_build_ms: the cost of bringing the accel up to date
+  return reupload(stream, err);
+}
+
 void MeshScene::next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1) {
   *e0 = *e1 = nullptr;
   if (trace_events_used_ + 2 > 8192) return;  // very long renders: the tail is simply not timed per kernel

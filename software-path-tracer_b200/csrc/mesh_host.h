@@ -35,6 +35,9 @@ class MeshScene {
   void set_materials(const cudapt_material* m, uint32_t n);
   bool has_host_mesh() const { return !indices_.empty(); }
   bool build_and_upload(std::string* err);
+  // Same topology, moved vertices: refit the BVH on the host (no rebuild) and upload it again.
+  bool update_vertices(const float* vertices, uint32_t nv, cudaStream_t stream, std::string* err);
+  double refit_ms = 0.0;
   // H2D copy of the packed scene (nodes, triangles, materials, lights) from pinned host memory.
   bool reupload(cudaStream_t stream, std::string* err);
   cudaError_t render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err);

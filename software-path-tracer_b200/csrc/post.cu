@@ -94,7 +94,58 @@ __global__ void __launch_bounds__(256) auto_exposure_kernel(const float* __restr
   }
 }
 
+// K6': fused multi-GPU read-back tail (SURVEY.md 8e "fusion opportunity", 7.2 K6): reduce-scatter + resolve +
+// gather in ONE kernel per rank over NVLink/NVSwitch peer memory.  Rank r owns the pixel slice
+// [begin, end); for each of its pixels it LOADS the float4 accumulation of every rank (its own from HBM, the others
+// through peer-mapped pointers = NVLink P2P reads), adds them in rank order (deterministic: ((a0 + a1) + a2) + ...,
+// the order a sequential host merge would use), runs the post-process stage and STORES the packed RGBA8 word -- and
+// optionally the summed float4 -- straight into the root rank's buffers (P2P writes).  Per rank (G-1)/G of one
+// buffer crosses NVLink inbound instead of the whole buffer funnelling into the root.
+constexpr int kMaxRanks = 16;
+struct PeerPtrs {
+  const float4* accum[kMaxRanks];
+};
+__global__ void __launch_bounds__(256) reduce_resolve_peers_kernel(const PeerPtrs peers, int n_ranks, uint32_t begin, uint32_t end,
+                                                                   float total_frames, float exposure, int tonemap, int srgb,
+                                                                   uint32_t* __restrict__ root_rgba, float4* __restrict__ root_accum) {
+  const uint32_t stride = gridDim.x * 256u;
+  for (uint32_t i = begin + blockIdx.x * 256u + threadIdx.x; i < end; i += stride) {
+    float4 a = peers.accum[0][i];
+    for (int g = 1; g < n_ranks; ++g) {
+      const float4 b = peers.accum[g][i];
+      a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+    }
+    if (root_accum) root_accum[i] = a;
+    float c[3] = {a.x / total_frames, a.y / total_frames, a.z / total_frames};
+    uint32_t b8[4];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      float v = c[k] * exposure;
+      v = tonemap_channel(v, tonemap);
+      v = clamp01(v);
+      if (srgb) v = clamp01(srgb_encode(v));
+      b8[k] = __float2uint_rz(v * 255.0f) & 0xFFu;
+    }
+    b8[3] = __float2uint_rz(clamp01(a.w / total_frames) * 255.0f) & 0xFFu;
+    root_rgba[i] = (b8[0] << 24) | (b8[1] << 16) | (b8[2] << 8) | b8[3];
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_reduce_resolve_peers(const float4* const* accum_by_rank, int n_ranks, uint32_t begin, uint32_t end,
+                                        uint32_t total_frames, float exposure, int tonemap, int srgb, uint32_t* root_rgba,
+                                        float4* root_accum, int sm_count, cudaStream_t stream) {
+  if (n_ranks < 1 || n_ranks > kMaxRanks) return cudaErrorInvalidValue;
+  if (end <= begin) return cudaSuccess;
+  PeerPtrs p{};
+  for (int g = 0; g < n_ranks; ++g) p.accum[g] = accum_by_rank[g];
+  const uint32_t want = (end - begin + 255u) / 256u;
+  const uint32_t cap = (uint32_t)sm_count * 8u;
+  reduce_resolve_peers_kernel<<<want < cap ? want : cap, 256, 0, stream>>>(p, n_ranks, begin, end, (float)total_frames, exposure,
+                                                                           tonemap, srgb, root_rgba, root_accum);
+  return cudaGetLastError();
+}
 
 uint32_t auto_exposure_partials(uint32_t n_pixels) { return (n_pixels + kLumBlock * kLumPerThread - 1) / (kLumBlock * kLumPerThread); }
 

@@ -72,13 +72,28 @@ static Scene grid(int n) {  // height field + axis-aligned flat walls (zero-thic
   return s;
 }
 
-static int check(const char* name, const Scene& sc, int n_rays, bool from_inside) {
+static int check(const char* name, Scene sc, int n_rays, bool from_inside, bool refit = false) {
   Bvh8 bvh;
   std::string err;
   const uint32_t nt = (uint32_t)sc.idx.size() / 3;
   if (!build_bvh8(sc.v.data(), (uint32_t)sc.v.size() / 3, sc.idx.data(), nt, nullptr, 4, &bvh, &err)) {
     std::printf("%s: build failed: %s\n", name, err.c_str());
     return 1;
+  }
+  if (refit) {  // move every vertex, refit (no rebuild) and validate the refitted tree exactly like a fresh one
+    for (float& c : sc.v) c += (rnd() - 0.5f) * 0.6f;
+    if (!refit_bvh8(sc.v.data(), (uint32_t)sc.v.size() / 3, sc.idx.data(), nt, &bvh, &err)) {
+      std::printf("%s: refit failed: %s\n", name, err.c_str());
+      return 1;
+    }
+    // the packed records must be exactly what a fresh build of the moved mesh would store
+    Bvh8 fresh;
+    if (!build_bvh8(sc.v.data(), (uint32_t)sc.v.size() / 3, sc.idx.data(), nt, nullptr, 4, &fresh, &err)) return 1;
+    for (uint32_t i = 0; i < nt; ++i)
+      if (std::memcmp(&fresh.tris[fresh.tri_of_prim[i]], &bvh.tris[bvh.tri_of_prim[i]], sizeof(PackedTri)) != 0) {
+        std::printf("%s: refit triangle record %u differs from a fresh build\n", name, i);
+        return 1;
+      }
   }
   // structural checks
   std::vector<uint8_t> seen(nt, 0);
@@ -153,6 +168,9 @@ int main(int argc, char** argv) {
   bad += check("grid-64", grid(64), n_rays, false);
   bad += check("tiny-1", soup(1, 1.f, 4.f), 200, true);
   bad += check("tiny-5", soup(5, 2.f, 4.f), 500, true);
+  bad += check("refit-soup-2k", soup(2000, 12.f, 1.5f), n_rays, true, true);
+  bad += check("refit-grid-64", grid(64), n_rays, false, true);
+  bad += check("refit-tiny-1", soup(1, 1.f, 4.f), 200, true, true);
   std::printf(bad ? "FAILED (%d)\n" : "OK\n", bad);
   return bad ? 1 : 0;
 }

@@ -181,3 +181,38 @@ def test_medium_heightfield_primary_hits_at_config_resolution(pt, oracle, scenes
     assert np.all(acc[..., 3] == 1) and np.isfinite(acc).all() and (acc[..., :3] >= 0).all()
     assert same_frac(acc, want) >= 0.999
     tr.close()
+
+
+def test_update_vertices_refit_equals_fresh_build(pt, oracle, scenes):
+    """moving the vertices and refitting (no rebuild) gives the image of a fresh build of the moved
+    mesh, bit for bit (the closest-hit rule does not depend on the acceleration structure), and equals the twin."""
+    W, H, N = 128, 72, 3
+    v, t, m, mats = scenes.heightfield(n_quads=48)
+    rng = np.random.default_rng(3)
+    v2 = (v + rng.normal(0.0, 0.05, v.shape)).astype(np.float32)
+    kw = dict(max_bounces=5, jitter=1, seed=21)
+    cfg = pt.default_config(rng_mode=1, samples_per_pass=3, **kw)
+    with pt.PathTracer(cfg) as tr:
+        tr.set_resolution(W, H)
+        tr.upload_mesh(v, t, m, mats)
+        tr.render(N)
+        before, _ = tr.read_accum()
+        tr.update_vertices(v2)
+        assert tr.stats().frame_count == 0  # accumulation restarted, like a scene change (CPT.cpp:122-131)
+        tr.render(N)
+        refit, fc = tr.read_accum()
+        prim_refit, t_refit = tr.read_primary_hits()
+        with pytest.raises(pt.CudaptError):
+            tr.update_vertices(v2[:-1])  # topology change is not an update
+    with pt.PathTracer(cfg) as tr:
+        tr.set_resolution(W, H)
+        tr.upload_mesh(v2, t, m, mats)
+        tr.render(N)
+        fresh, _ = tr.read_accum()
+        prim_fresh, t_fresh = tr.read_primary_hits()
+    assert fc == N
+    assert np.array_equal(bits(refit), bits(fresh))
+    assert np.array_equal(prim_refit, prim_fresh) and np.array_equal(bits(t_refit), bits(t_fresh))
+    assert same_frac(before, refit) < 0.9
+    want, _, _, _ = oracle.TwinMesh(v2, t, m, mats).render(oracle.twin_params(W, H, rng_mode=1, **kw), N)
+    assert same_frac(refit, want) >= 0.999
