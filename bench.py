@@ -40,6 +40,10 @@ WORKLOADS = {
     "c4": dict(desc="configs[3]: 20,000,002-triangle flattened rock field (BVH > L2), 1920x1080, 128 spp, depth 16",
                w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=16),
                fov=1.0, kind="mesh"),
+    "c5": dict(desc="configs[4]: the 1,002,528-triangle scene at 3840x2160, 1024 spp IN TOTAL sharded over the ranks "
+                    "(sample ranges), accumulation combined at the read-back boundary",
+               w=3840, h=2160, spp=1024, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=8),
+               fov=1.0, kind="mesh", strong=True),
 }
 DEFAULT_WORKLOAD = "c3"
 
@@ -58,7 +62,7 @@ def build_scene(scenes, wl):
     name = wl["name"]
     if name == "c2":
         v, t, m, mats = scenes.cornell_box()
-    elif name == "c3":
+    elif name in ("c3", "c5"):
         v, t, m, mats = scenes.heightfield()
     else:
         v, t, m, mats = scenes.rock_field()
@@ -206,6 +210,9 @@ def main():
     wl = dict(WORKLOADS[args.workload], name=args.workload)
     if args.spp:
         wl["spp"] = args.spp
+    strong = bool(wl.get("strong"))
+    if strong:  # total work fixed: every rank renders its share of the samples
+        wl["spp"] = max(1, wl["spp"] // world)
     scenes = importlib.import_module("software-path-tracer_b200.scenes")
 
     if args.impl == "reference":
@@ -268,7 +275,7 @@ def main():
         with torch.cuda.stream(stream):
             if fused:
                 dist.all_reduce(tick)   # stream-ordered rendezvous: every rank's render is complete
-                tr.reduce_resolve_peers(peer_accum, rank, spp * world, root_rgba, root_accum)
+                tr.reduce_resolve_peers(peer_accum, rank, spp * world, root_rgba, None)  # image only: the merged floats stay distributed
                 dist.all_reduce(tick)   # every rank's slice has landed in the root's buffers
             else:
                 part.reduce_accum(accum_t, dst=0)
@@ -299,6 +306,7 @@ def main():
     launches0 = tr.stats().kernel_launches
     sampler = ClockSampler(local_rank) if rank == 0 else None
     time.sleep(0.25) if sampler else None
+    sync_all()  # ranks enter the timed region together (rank 0 has just spent 0.25 s starting the clock sampler)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_wall0 = time.time()
     for k in range(args.steps):
@@ -311,6 +319,8 @@ def main():
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
     step_ms = [a.elapsed_time(b) for a, b in ev]
+    if os.environ.get("BENCH_DEBUG"):
+        print(f"[rank {rank}] step_ms {step_ms}", file=sys.stderr, flush=True)
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=f"cuda:{local_rank}")
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
@@ -354,6 +364,24 @@ def main():
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = world * paths_per_step * args.steps / float(e2e_s.item()) / 1e6
 
+    # the read-back tail alone (N > 1): CUDA events on the library's stream, max over ranks
+    tail_info = None
+    if world > 1:
+        sync_all()
+        te = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+        for a, b in te:
+            a.record(stream)
+            tail()
+            b.record(stream)
+        sync_all()
+        tms = torch.tensor([sorted(a.elapsed_time(b) for a, b in te)[len(te) // 2]], dtype=torch.float64,
+                           device=f"cuda:{local_rank}")
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        tail_info = {"kind": args.tail, "median_ms": float(tms.item()), "accum_bytes_per_rank": int(n_px * 16),
+                     "note": "fused: 2 stream-ordered 4-byte all-reduces (rendezvous) + one reduce-scatter/resolve/gather "
+                             "kernel per rank over NVLink peer memory" if fused else
+                             "ncclReduce(sum) of the float accumulation buffer to rank 0 (resolve not included)"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -363,7 +391,8 @@ def main():
     roof = roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src)
     line = {
         "metric": "Msamples/s (paths/s)", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong" if strong else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "name": wl["name"], "width": W, "height": H, "spp_per_gpu": spp,
                    "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
@@ -379,6 +408,8 @@ def main():
         "clocks": clocks,
         "roofline": roof,
     }
+    if tail_info:
+        line["tail"] = tail_info
     if world == 1 and not args.no_cpu_baseline:
         n, sec, rays, kind, cores, desc = cpu_sample(wl, scene)
         line["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Msamples/s", "cores": cores, "kind": kind,
