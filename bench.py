@@ -33,16 +33,16 @@ WORKLOADS = {
                w=640, h=360, spp=16, cfg=dict(), fov=1.0, kind="spheres"),
     "c2": dict(desc="configs[1]: Cornell box mesh (diffuse+mirror+dielectric), 1280x720, 256 spp, area-light NEE, depth 8",
                w=1280, h=720, spp=256, cfg=dict(rng_mode=1, max_bounces=8, sky_scale=0.0, jitter=1, nee=1, seed=2,
-                                                samples_per_pass=16), fov=0.36, kind="mesh"),
+                                                samples_per_pass=256), fov=0.36, kind="mesh"),
     "c3": dict(desc="configs[2]: 1,002,528-triangle fBm height field, GGX-coated, 1920x1080, 64 spp, depth 8",
-               w=1920, h=1080, spp=64, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=16),
+               w=1920, h=1080, spp=64, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=64),
                fov=1.0, kind="mesh"),
     "c4": dict(desc="configs[3]: 20,000,002-triangle flattened rock field (BVH > L2), 1920x1080, 128 spp, depth 16",
-               w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=16),
+               w=1920, h=1080, spp=128, cfg=dict(rng_mode=1, max_bounces=16, jitter=1, seed=4, samples_per_pass=128),
                fov=1.0, kind="mesh"),
     "c5": dict(desc="configs[4]: the 1,002,528-triangle scene at 3840x2160, 1024 spp IN TOTAL sharded over the ranks "
                     "(sample ranges), accumulation combined at the read-back boundary",
-               w=3840, h=2160, spp=1024, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=8),
+               w=3840, h=2160, spp=1024, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=32),
                fov=1.0, kind="mesh", strong=True),
 }
 DEFAULT_WORKLOAD = "c3"
@@ -198,6 +198,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
+    ap.add_argument("--spp-pass", type=int, default=0, help="override samples per wavefront pass (debug)")
     ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],
                     help="N > 1 read-back tail: 'fused' = one reduce-scatter+resolve+gather kernel per rank over NVLink "
                          "peer memory (cudapt_reduce_resolve_peers); 'nccl' = NCCL reduce of the float buffer to rank 0")
@@ -210,6 +211,8 @@ def main():
     wl = dict(WORKLOADS[args.workload], name=args.workload)
     if args.spp:
         wl["spp"] = args.spp
+    if args.spp_pass:
+        wl["cfg"] = dict(wl["cfg"], samples_per_pass=args.spp_pass)
     strong = bool(wl.get("strong"))
     if strong:  # total work fixed: every rank renders its share of the samples
         wl["spp"] = max(1, wl["spp"] // world)

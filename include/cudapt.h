@@ -78,7 +78,8 @@ typedef struct cudapt_config {
   uint32_t seed;             /* Philox key word 1 */
   int32_t jitter;            /* default 0: sub-pixel jitter (Philox mode only); 0 = reference corner sampling */
   int32_t nee;               /* default 0: next-event estimation on emissive triangles (mesh integrator) */
-  int32_t samples_per_pass;  /* default 1: samples of every pixel traced together by the wavefront */
+  int32_t samples_per_pass;  /* default 1, <= 256: samples of every pixel traced together by the wavefront (136 B of path
+                                state per sample and pixel: large passes amortise the near-empty tail bounces) */
 } cudapt_config;
 
 typedef struct cudapt_stats {
