@@ -214,7 +214,19 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     return cudaErrorInvalidValue;
   }
   const uint32_t n_pixels = a.im.width * a.im.height;
-  const uint32_t S = std::max(1u, a.samples_per_pass);
+  uint32_t S = std::max(1u, std::min(a.samples_per_pass, a.n_frames));
+  // 148 B of state + queues per path: keep a pass within 3/4 of the memory that is free (or already ours), and its
+  // path ids within 32 bits
+  {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+      const size_t ours = (size_t)dev_->state_paths * 148u;
+      const size_t budget = (free_b + ours) / 4u * 3u;
+      const size_t fit = budget / ((size_t)n_pixels * 148u);
+      S = (uint32_t)std::max<size_t>(1, std::min<size_t>(S, fit));
+    }
+    S = (uint32_t)std::min<uint64_t>(S, 0xFFFFFFFFull / n_pixels);
+  }
   const uint32_t max_b = (uint32_t)a.ip.max_bounces;
   cudaError_t e = ensure_state(dev_, n_pixels * S, max_b);
   if (e != cudaSuccess) {

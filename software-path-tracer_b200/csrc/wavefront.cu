@@ -142,15 +142,24 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
   const uint32_t rounds = (n + stride - 1) / stride;
   uint32_t n_shades = 0, n_paths = 0;
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  // Two-deep software pipeline over the dependent gathers queue -> hit -> triangle -> material: the queue entry is
+  // fetched two rounds ahead and the hit record one round ahead, so a round starts with both in registers and its
+  // critical path is (ray state | triangle) -> material instead of four dependent loads (profiles/r01_notes.md:
+  // the kernel was latency bound, long_scoreboard 7.2 per issue at 50 % issue utilisation).
+  uint32_t path_1 = i < n ? qin[i] : 0u;                    // entry of this round
+  uint32_t path_2 = i + stride < n ? qin[i + stride] : 0u;  // entry of the next round
+  uint2 hit_1 = st.hit[path_1];
   for (uint32_t k = 0; k < rounds; ++k, i += stride) {
     bool cont = false, shadow = false;
-    uint32_t path = 0;
+    const uint32_t path = path_1;
+    const uint2 h = hit_1;
+    path_1 = path_2;
+    path_2 = (k + 2 < rounds && i + 2 * stride < n) ? qin[i + 2 * stride] : 0u;
+    if (k + 1 < rounds) hit_1 = st.hit[path_1];  // path_1 was loaded a round ago: no stall here
     if (i < n) {
-      path = qin[i];
       const uint32_t s = path / p.n_pixels;
       const uint32_t pixel = path - s * p.n_pixels;
       const uint32_t frame = p.first_frame + s * p.frame_stride;
-      const uint2 h = st.hit[path];
       const float t = __uint_as_float(h.x);
       const float4 o4 = st.ray_o[path], d4 = st.ray_d[path];
       const float4 thr4 = a.bounce == 0 ? make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(kFlagSpecular)) : st.thr[path];
