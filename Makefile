@@ -10,7 +10,7 @@ CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace
 HDR      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cudapt.h
 OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o
 
-all: $(PKG)/libcudapt.so oracle host
+all: $(PKG)/libcudapt.so oracle host build/cudapt_cli
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDR)
 	$(NVCC) $(NVFLAGS) -dc -o $@ $< 2> $@.ptxas.log || (cat $@.ptxas.log; false)
@@ -36,6 +36,11 @@ build/headless_compare: $(PKG)/host/CUDAPathTracer.cpp $(PKG)/host/CUDAPathTrace
 	mkdir -p build
 	$(CXX) -std=gnu++23 -O2 -w $(REFINC) -Iinclude -I$(PKG)/host -o $@ $(PKG)/host/CUDAPathTracer.cpp tests/cpp/headless_compare.cpp \
 	    -L$(PKG) -lcudapt -Loracle/_ref -lref_render -Wl,-rpath,'$$ORIGIN/../$(PKG):$$ORIGIN/../oracle/_ref'
+
+# headless command-line front door, plain C over the C ABI
+build/cudapt_cli: tools/cudapt_cli.c include/cudapt.h $(PKG)/libcudapt.so
+	mkdir -p build
+	$(CC) -std=c99 -O2 -Wall -Iinclude -o $@ tools/cudapt_cli.c -L$(PKG) -lcudapt -Wl,-rpath,'$$ORIGIN/../$(PKG)'
 
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.ptxas.log $(PKG)/libcudapt.so

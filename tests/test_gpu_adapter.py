@@ -27,3 +27,31 @@ def test_adapter_sources_mirror_the_reference_interface():
                  "get_settings() const override", "get_backend_name() const override",
                  "get_backend_type() const override", "get_render_result() override"]:
         assert name in hdr, name
+
+
+@pytest.mark.gpu
+def test_cli_writes_the_reference_image(built, pt, oracle, scenes, tmp_path):
+    """tools/cudapt_cli.c (plain C over the C ABI): the App scene at 96x54x3 spp must give the reference's image."""
+    import subprocess
+    exe = os.path.join(ROOT, "build", "cudapt_cli")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", ROOT, "build/cudapt_cli"], check=True, capture_output=True)
+    out = tmp_path / "app.ppm"
+    r = subprocess.run([exe, "--size", "96x54", "--spp", "3", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = out.read_bytes()
+    head = b"P6\n96 54\n255\n"
+    assert raw.startswith(head)
+    import numpy as np
+    rgb = np.frombuffer(raw[len(head):], np.uint8).reshape(54, 96, 3)
+    want, _, _, _ = oracle.twin_render_spheres(oracle.twin_params(96, 54), scenes.app_spheres(), 3)
+    w = oracle.twin_resolve_rgba8(want, 3)
+    want_rgb = np.stack([(w >> 24) & 0xFF, (w >> 16) & 0xFF, (w >> 8) & 0xFF], -1).astype(np.uint8)
+    assert (rgb == want_rgb).all(axis=-1).mean() >= 0.9999
+    # an OBJ through the mesh integrator, tone-mapped
+    obj = tmp_path / "quad.obj"
+    obj.write_text("v -2 -2 5\nv 2 -2 5\nv 2 2 5\nv -2 2 5\nf 1 2 3 4\n")
+    out2 = tmp_path / "quad.pfm"
+    r = subprocess.run([exe, "--obj", str(obj), "--size", "32x18", "--spp", "4", "--out", str(out2)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert out2.read_bytes().startswith(b"PF\n32 18\n-1.0\n")
