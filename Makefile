@@ -6,7 +6,7 @@ CSRC     := $(PKG)/csrc
 NVFLAGS  := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
             -fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
             -Xcompiler -fPIC,-O2,-ffp-contract=off -Xptxas -v
-CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace_bvh.cu $(CSRC)/wavefront.cu $(CSRC)/post.cu
+CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace_bvh.cu $(CSRC)/wavefront.cu $(CSRC)/post.cu $(CSRC)/refit.cu
 HDR      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cudapt.h
 OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o
 
@@ -15,7 +15,7 @@ all: $(PKG)/libcudapt.so oracle host build/cudapt_cli
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDR)
 	$(NVCC) $(NVFLAGS) -dc -o $@ $< 2> $@.ptxas.log || (cat $@.ptxas.log; false)
 
-$(CSRC)/bvh_build.o: $(CSRC)/bvh_build.cpp $(CSRC)/bvh8.h
+$(CSRC)/bvh_build.o: $(CSRC)/bvh_build.cpp $(CSRC)/bvh8.h $(CSRC)/bvh8_refit.h
 	$(CXX) -std=c++17 -O2 -fPIC -ffp-contract=off -pthread -c -o $@ $<
 
 $(PKG)/libcudapt.so: $(OBJ)

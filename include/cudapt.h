@@ -144,6 +144,10 @@ int cudapt_reupload_scene(cudapt_ctx* ctx);
  * Because the closest-hit rule does not depend on the acceleration structure, the image after an update is
  * bit-identical to a fresh build of the moved mesh. */
 int cudapt_update_vertices(cudapt_ctx* ctx, const float* vertices, uint32_t nv);
+/* Test hook: FNV-1a checksums of the device-resident node and packed-triangle arrays (the refit runs on the device,
+ * csrc/refit.cu; with CUDAPT_REFIT_HOST=1 in the environment the host implementation of the same code runs instead
+ * and must leave the same bytes). */
+int cudapt_debug_accel_checksum(cudapt_ctx* ctx, uint64_t* nodes_sum, uint64_t* tris_sum);
 
 /* Environment map replacing the procedural sky on a miss (reference anchor: the commented-out
  * Scene::setEnvironmentMap, libs/render/src/Scene.cpp:124-169, and the SkyBox of Scene.h:268-278).  rgb is a

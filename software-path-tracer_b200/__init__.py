@@ -69,7 +69,7 @@ EXPORTS = [
     "cudapt_default_config", "cudapt_default_camera", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
-    "cudapt_reupload_scene", "cudapt_update_vertices",
+    "cudapt_reupload_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
     "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
@@ -111,6 +111,7 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_build_accel.argtypes = [vp]
     lib.cudapt_reupload_scene.argtypes = [vp]
     lib.cudapt_update_vertices.argtypes = [vp, vp, u32]
+    lib.cudapt_debug_accel_checksum.argtypes = [vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
     lib.cudapt_reset.argtypes = [vp]
     lib.cudapt_render.argtypes = [vp, u32]
     lib.cudapt_synchronize.argtypes = [vp]
@@ -249,6 +250,11 @@ class PathTracer:
     def update_vertices(self, vertices):
         v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
         self._chk(self._lib.cudapt_update_vertices(self._h, _p(v), len(v)))
+
+    def accel_checksum(self):
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        self._chk(self._lib.cudapt_debug_accel_checksum(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     def reupload_scene(self):
         self._chk(self._lib.cudapt_reupload_scene(self._h))

@@ -363,7 +363,10 @@ int cudapt_update_vertices(cudapt_ctx* ctx, const float* vertices, uint32_t nv) 
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // the pinned staging buffer may still be in flight
   std::string err;
-  if (!ctx->mesh.update_vertices(vertices, nv, ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_update_vertices: %s", err.c_str());
+  uint64_t launches = 0;
+  const bool ok = ctx->mesh.update_vertices(vertices, nv, ctx->stream, &launches, &err);
+  ctx->launches += launches;
+  if (!ok) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_update_vertices: %s", err.c_str());
   return restart_accumulation(ctx);
 }
 
@@ -727,5 +730,14 @@ int cudapt_ipc_close(cudapt_ctx* ctx, void* device_ptr) {
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   CU_TRY(ctx, cudaIpcCloseMemHandle(device_ptr));
+  return CUDAPT_OK;
+}
+
+int cudapt_debug_accel_checksum(cudapt_ctx* ctx, uint64_t* nodes_sum, uint64_t* tris_sum) {
+  if (!ctx || !nodes_sum || !tris_sum) return CUDAPT_ERR_INVALID;
+  if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_debug_accel_checksum: no built mesh scene");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  std::string err;
+  if (!ctx->mesh.accel_checksum(ctx->stream, nodes_sum, tris_sum, &err)) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_debug_accel_checksum: %s", err.c_str());
   return CUDAPT_OK;
 }

@@ -56,6 +56,7 @@ struct Bvh8 {
   std::vector<PackedTri> tris;       // leaf order
   std::vector<uint32_t> tri_of_prim; // caller index -> leaf-order index
   uint32_t max_depth = 0;            // depth of the 8-wide tree (root = 1)
+  std::vector<uint32_t> level_start; // nodes are emitted breadth-first: level d (0 = root) is [level_start[d], level_start[d+1])
   float world_lo[3] = {0, 0, 0}, world_hi[3] = {0, 0, 0};
   double sah_cost = 0.0;
 };

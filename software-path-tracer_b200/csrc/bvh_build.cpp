@@ -9,6 +9,7 @@
 //   5. breadth-first emission: internal children of a node are contiguous (indexable by popcount of
 //      imask), leaf triangles of a node are contiguous (indexable by a 5-bit offset).
 #include "bvh8.h"
+#include "bvh8_refit.h"
 
 #include <algorithm>
 #include <atomic>
@@ -151,75 +152,20 @@ struct Child {
   bool leaf;
 };
 
-// Step 4 of the build, shared with refit_bvh8(): per-axis power-of-two grid anchored at the node box minimum and
-// outward-rounded 8-bit child bounds (exact arithmetic in double, so p + q * 2^e always encloses the child box).
-void quantise_node(const Box& nb, const Box* slot_box, const bool* slot_used, Bvh8Node* Np) {
-  Bvh8Node& N = *Np;
-  int ex[3];
-  for (int k = 0; k < 3; ++k) {
-    N.p[k] = nb.lo[k];
-    const double ext = (double)nb.hi[k] - (double)nb.lo[k];
-    int e = -60;
-    if (ext > 0.0) {
-      int kk;
-      (void)std::frexp(ext / 255.0, &kk);
-      e = kk;
-    }
-    ex[k] = std::min(std::max(e, -125), 126);
-  }
-  uint8_t* qlo[3] = {N.qlo_x, N.qlo_y, N.qlo_z};
-  uint8_t* qhi[3] = {N.qhi_x, N.qhi_y, N.qhi_z};
-  for (int k = 0; k < 3; ++k) {
-    for (;;) {
-      const double scale = std::ldexp(1.0, ex[k]);
-      bool ok = true;
-      for (int s = 0; s < 8 && ok; ++s) {
-        if (!slot_used[s]) {
-          qlo[k][s] = 255;  // empty slot: inverted box, never hit
-          qhi[k][s] = 0;
-          continue;
-        }
-        double l = std::floor(((double)slot_box[s].lo[k] - (double)N.p[k]) / scale);
-        double h = std::ceil(((double)slot_box[s].hi[k] - (double)N.p[k]) / scale);
-        while ((double)N.p[k] + l * scale > (double)slot_box[s].lo[k]) l -= 1.0;
-        while ((double)N.p[k] + h * scale < (double)slot_box[s].hi[k]) h += 1.0;
-        l = std::max(l, 0.0);
-        if (h > 255.0) {
-          ok = false;
-          break;
-        }
-        qlo[k][s] = (uint8_t)l;
-        qhi[k][s] = (uint8_t)std::max(h, 0.0);
-      }
-      if (ok) break;
-      ++ex[k];
-    }
-    N.e[k] = (uint8_t)(ex[k] + 127);
-  }
+// Step 4 of the build and the triangle packing live in bvh8_refit.h (shared with the GPU refit kernels).
+void quantise_node(const Box& nb, const Box* slot_box, const bool* slot_used, Bvh8Node* N) {
+  Box3 b3, sb[8];
+  std::memcpy(&b3, &nb, sizeof(b3));
+  for (int s = 0; s < 8; ++s) std::memcpy(&sb[s], &slot_box[s], sizeof(Box3));
+  quantise_node_hd(b3, sb, slot_used, N);
 }
-
-// Packed record + padded box of one triangle (what the kernels intersect, see build_bvh8()).
 void pack_triangle(const float* vertices, const uint32_t* indices, uint32_t i, uint32_t material, PackedTri* T, float* lo3,
                    float* hi3) {
-  const float* a = vertices + 3 * (size_t)indices[3 * (size_t)i + 0];
-  const float* b = vertices + 3 * (size_t)indices[3 * (size_t)i + 1];
-  const float* c = vertices + 3 * (size_t)indices[3 * (size_t)i + 2];
-  for (int k = 0; k < 3; ++k) {
-    T->v0[k] = a[k];
-    T->e1[k] = b[k] - a[k];  // single rounding; the kernels (and the CPU oracle) intersect (v0, e1, e2)
-    T->e2[k] = c[k] - a[k];
-    // box of the triangle the kernels actually see: v0, v0+e1, v0+e2 (+ the caller's vertices), padded
-    const float b2 = a[k] + T->e1[k], c2 = a[k] + T->e2[k];
-    float lo = std::min(std::min(a[k], b[k]), std::min(c[k], std::min(b2, c2)));
-    float hi = std::max(std::max(a[k], b[k]), std::max(c[k], std::max(b2, c2)));
-    const float pad = 4e-7f * std::max(std::fabs(lo), std::fabs(hi)) + 1e-30f;
-    lo3[k] = lo - pad;
-    hi3[k] = hi + pad;
-  }
-  T->prim = i;
-  T->material = material;
-  T->pad = 0;
+  Box3 b;
+  pack_triangle_hd(vertices, indices, i, material, T, &b);
+  for (int k = 0; k < 3; ++k) lo3[k] = b.lo[k], hi3[k] = b.hi[k];
 }
+static_assert(sizeof(Box) == sizeof(Box3), "Box layout");
 
 }  // namespace
 
@@ -257,6 +203,7 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
   out->tris.reserve(nt);
   out->tri_of_prim.assign(nt, 0u);
   out->max_depth = 0;
+  out->level_start.clear();
   out->sah_cost = 0.0;
   for (int k = 0; k < 3; ++k) out->world_lo[k] = n2[0].box.lo[k], out->world_hi[k] = n2[0].box.hi[k];
   const double root_area = std::max((double)n2[0].box.area(), 1e-30);
@@ -271,6 +218,7 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     const Work w = queue.front();
     queue.pop_front();
     out->max_depth = std::max(out->max_depth, w.depth);
+    if (out->level_start.size() < w.depth) out->level_start.push_back(w.node8);  // breadth-first: first node of the level
     std::vector<Child> ch;
     if (n2[w.node2].count) {
       ch.push_back({w.node2, n2[w.node2].box, true});  // whole scene is one leaf
@@ -384,7 +332,7 @@ bool refit_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     *err = "refit: triangle count differs from the built scene";
     return false;
   }
-  std::vector<Box> tri_box(nt);  // by leaf-order index
+  std::vector<Box3> tri_box(nt);  // by leaf-order index
   for (uint32_t k = 0; k < nt; ++k) {
     PackedTri& T = bvh->tris[k];
     const uint32_t prim = T.prim, mat = T.material;
@@ -392,34 +340,11 @@ bool refit_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
       *err = "refit: corrupt triangle record";
       return false;
     }
-    pack_triangle(vertices, indices, prim, mat, &T, tri_box[k].lo, tri_box[k].hi);
+    pack_triangle_hd(vertices, indices, prim, mat, &T, &tri_box[k]);
   }
   const size_t nn = bvh->nodes.size();
-  std::vector<Box> node_box(nn);
-  for (size_t i = nn; i-- > 0;) {
-    Bvh8Node& N = bvh->nodes[i];
-    Box slot_box[8], nb;
-    bool slot_used[8];
-    for (int s = 0; s < 8; ++s) {
-      slot_used[s] = false;
-      if (N.imask & (1u << s)) {
-        const uint32_t child = N.child_base + (uint32_t)__builtin_popcount(N.imask & ((1u << s) - 1u));
-        slot_box[s] = node_box[child];
-        slot_used[s] = true;
-      } else {
-        for (uint32_t j = 0; j < 3; ++j) {
-          const uint32_t bit = 8 * j + (uint32_t)s;
-          if (!(N.tri_valid & (1u << bit))) continue;
-          const uint32_t t = N.tri_base + (uint32_t)__builtin_popcount(N.tri_valid & ((1u << bit) - 1u));
-          slot_box[s].grow(tri_box[t]);
-          slot_used[s] = true;
-        }
-      }
-      if (slot_used[s]) nb.grow(slot_box[s]);
-    }
-    quantise_node(nb, slot_box, slot_used, &N);
-    node_box[i] = nb;
-  }
+  std::vector<Box3> node_box(nn);
+  for (size_t i = nn; i-- > 0;) refit_node_hd(bvh->nodes.data(), (uint32_t)i, node_box.data(), tri_box.data());
   for (int k = 0; k < 3; ++k) bvh->world_lo[k] = node_box[0].lo[k], bvh->world_hi[k] = node_box[0].hi[k];
   return true;
 }

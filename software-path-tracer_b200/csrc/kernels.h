@@ -45,6 +45,11 @@ cudaError_t launch_reduce_resolve_peers(const float4* const* accum_by_rank, int 
                                         uint32_t total_frames, float exposure, int tonemap, int srgb, uint32_t* root_rgba,
                                         float4* root_accum, int sm_count, cudaStream_t stream);
 
+// refit.cu: BVH8 refit on the device (same arithmetic as the host builder, bvh8_refit.h)
+cudaError_t launch_refit(const float* d_vertices, const uint32_t* d_indices, uint32_t nt, void* d_nodes, void* d_tris,
+                         void* d_tri_box, void* d_node_box, const uint32_t* level_start, uint32_t n_levels, uint32_t n_nodes,
+                         uint64_t* launches, cudaStream_t stream);
+
 // ---- mesh wavefront integrator (wavefront.cu, trace_bvh.cu) -------------------------------------------
 // Path state lives in HBM as structure-of-arrays indexed by PATH ID = sample_in_pass * n_pixels + pixel;
 // queues hold 4-byte path ids, so compaction moves indices only.

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -21,6 +22,13 @@ struct MeshDevice {
   uint32_t* d_lights = nullptr;
   void* h_pinned = nullptr;  // nodes | tris, pinned, for cudapt_reupload_scene
   size_t pinned_bytes = 0;
+  bool staging_stale = false;  // the device copy was refitted in place; refresh h_pinned before re-uploading from it
+  // device refit (refit.cu): caller-order vertices and indices, per-triangle and per-node boxes
+  float* d_vertices = nullptr;
+  uint32_t* d_indices = nullptr;
+  void* d_tri_box = nullptr;
+  void* d_node_box = nullptr;
+  void* h_pinned_vertices = nullptr;
   // wavefront state
   WavefrontState st{};
   uint32_t state_paths = 0;     // capacity in paths
@@ -37,6 +45,11 @@ struct MeshDevice {
   void free_scene() {
     cudaFree(d_nodes), cudaFree(d_tris), cudaFree(d_materials), cudaFree(d_lights);
     d_nodes = nullptr, d_tris = nullptr, d_materials = nullptr, d_lights = nullptr;
+    cudaFree(d_vertices), cudaFree(d_indices), cudaFree(d_tri_box), cudaFree(d_node_box);
+    d_vertices = nullptr, d_indices = nullptr, d_tri_box = nullptr, d_node_box = nullptr;
+    if (h_pinned_vertices) cudaFreeHost(h_pinned_vertices);
+    h_pinned_vertices = nullptr;
+    staging_stale = false;
     if (h_pinned) cudaFreeHost(h_pinned);
     h_pinned = nullptr;
     pinned_bytes = 0;
@@ -127,6 +140,7 @@ bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
     *err = "no built scene";
     return false;
   }
+  if (dev_->staging_stale && !refresh_staging(stream, err)) return false;
   const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
   MH_TRY(cudaMemcpyAsync(dev_->d_nodes, dev_->h_pinned, nb, cudaMemcpyHostToDevice, stream));
   MH_TRY(cudaMemcpyAsync(dev_->d_tris, (char*)dev_->h_pinned + nb, tb, cudaMemcpyHostToDevice, stream));
@@ -138,7 +152,7 @@ bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
   return true;
 }
 
-bool MeshScene::update_vertices(const float* v, uint32_t nv, cudaStream_t stream, std::string* err) {
+bool MeshScene::update_vertices(const float* v, uint32_t nv, cudaStream_t stream, uint64_t* launches, std::string* err) {
   if (!dev_ || !dev_->h_pinned) {
     *err = "no built scene";
     return false;
@@ -150,13 +164,72 @@ bool MeshScene::update_vertices(const float* v, uint32_t nv, cudaStream_t stream
   const auto t0 = std::chrono::steady_clock::now();
   vertices_.assign(v, v + 3 * (size_t)nv);
   Bvh8& bvh = dev_->bvh;
-  if (!refit_bvh8(vertices_.data(), nv, indices_.data(), (uint32_t)(indices_.size() / 3), &bvh, err)) return false;
-  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
-  std::memcpy(dev_->h_pinned, bvh.nodes.data(), nb);
-  std::memcpy((char*)dev_->h_pinned + nb, bvh.tris.data(), tb);
+  const uint32_t nt = (uint32_t)(indices_.size() / 3);
+  const char* force_host = std::getenv("CUDAPT_REFIT_HOST");
+  if (force_host && force_host[0] == '1') {
+    // host refit (the same code, bvh8_refit.h): kept as the cross-check of the device kernels
+    if (dev_->staging_stale && !refresh_staging(stream, err)) return false;
+    if (!refit_bvh8(vertices_.data(), nv, indices_.data(), nt, &bvh, err)) return false;
+    const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
+    std::memcpy(dev_->h_pinned, bvh.nodes.data(), nb);
+    std::memcpy((char*)dev_->h_pinned + nb, bvh.tris.data(), tb);
+    refit_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    build_ms = refit_ms;
+    return reupload(stream, err);
+  }
+  // device refit: only the vertex positions cross PCIe
+  const size_t vb = sizeof(float) * 3 * (size_t)nv;
+  if (!dev_->d_vertices) {
+    MH_TRY(cudaMalloc(&dev_->d_vertices, vb));
+    MH_TRY(cudaMalloc(&dev_->d_indices, sizeof(uint32_t) * indices_.size()));
+    MH_TRY(cudaMalloc(&dev_->d_tri_box, 24 * (size_t)nt));
+    MH_TRY(cudaMalloc(&dev_->d_node_box, 24 * bvh.nodes.size()));
+    MH_TRY(cudaMallocHost(&dev_->h_pinned_vertices, vb));
+    MH_TRY(cudaMemcpyAsync(dev_->d_indices, indices_.data(), sizeof(uint32_t) * indices_.size(), cudaMemcpyHostToDevice, stream));
+  }
+  std::memcpy(dev_->h_pinned_vertices, vertices_.data(), vb);
+  MH_TRY(cudaMemcpyAsync(dev_->d_vertices, dev_->h_pinned_vertices, vb, cudaMemcpyHostToDevice, stream));
+  MH_TRY(launch_refit(dev_->d_vertices, dev_->d_indices, nt, dev_->d_nodes, dev_->d_tris, dev_->d_tri_box, dev_->d_node_box,
+                      bvh.level_start.data(), (uint32_t)bvh.level_start.size(), (uint32_t)bvh.nodes.size(), launches, stream));
+  MH_TRY(cudaStreamSynchronize(stream));
+  dev_->staging_stale = true;
   refit_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   build_ms = refit_ms;  // reported as accel_build_ms: the cost of bringing the accel up to date
-  return reupload(stream, err);
+  return true;
+}
+
+// After a device refit the pinned staging copy (and the host Bvh8) lag behind the device: fetch them back.
+bool MeshScene::refresh_staging(cudaStream_t stream, std::string* err) {
+  Bvh8& bvh = dev_->bvh;
+  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
+  MH_TRY(cudaMemcpyAsync(dev_->h_pinned, dev_->d_nodes, nb, cudaMemcpyDeviceToHost, stream));
+  MH_TRY(cudaMemcpyAsync((char*)dev_->h_pinned + nb, dev_->d_tris, tb, cudaMemcpyDeviceToHost, stream));
+  MH_TRY(cudaStreamSynchronize(stream));
+  std::memcpy(bvh.nodes.data(), dev_->h_pinned, nb);
+  std::memcpy(bvh.tris.data(), (char*)dev_->h_pinned + nb, tb);
+  dev_->staging_stale = false;
+  return true;
+}
+
+// Debug/test hook: FNV-1a over the device copies of the node and triangle arrays.
+bool MeshScene::accel_checksum(cudaStream_t stream, uint64_t* nodes_sum, uint64_t* tris_sum, std::string* err) {
+  if (!dev_ || !dev_->d_nodes) {
+    *err = "no built scene";
+    return false;
+  }
+  const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
+  std::vector<unsigned char> buf(std::max(nb, tb));
+  auto fnv = [&](size_t n) {
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < n; ++i) h = (h ^ buf[i]) * 1099511628211ull;
+    return h;
+  };
+  MH_TRY(cudaStreamSynchronize(stream));
+  MH_TRY(cudaMemcpy(buf.data(), dev_->d_nodes, nb, cudaMemcpyDeviceToHost));
+  *nodes_sum = fnv(nb);
+  MH_TRY(cudaMemcpy(buf.data(), dev_->d_tris, tb, cudaMemcpyDeviceToHost));
+  *tris_sum = fnv(tb);
+  return true;
 }
 
 void MeshScene::next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1) {

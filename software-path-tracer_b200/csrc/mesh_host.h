@@ -36,7 +36,9 @@ class MeshScene {
   bool has_host_mesh() const { return !indices_.empty(); }
   bool build_and_upload(std::string* err);
   // Same topology, moved vertices: refit the BVH on the host (no rebuild) and upload it again.
-  bool update_vertices(const float* vertices, uint32_t nv, cudaStream_t stream, std::string* err);
+  // (on the device, refit.cu; CUDAPT_REFIT_HOST=1 selects the host implementation of the same code).
+  bool update_vertices(const float* vertices, uint32_t nv, cudaStream_t stream, uint64_t* launches, std::string* err);
+  bool accel_checksum(cudaStream_t stream, uint64_t* nodes_sum, uint64_t* tris_sum, std::string* err);
   double refit_ms = 0.0;
   // H2D copy of the packed scene (nodes, triangles, materials, lights) from pinned host memory.
   bool reupload(cudaStream_t stream, std::string* err);
@@ -49,6 +51,7 @@ class MeshScene {
   double collect_trace_ms();
 
  private:
+  bool refresh_staging(cudaStream_t stream, std::string* err);
   std::vector<float> vertices_;
   std::vector<uint32_t> indices_;
   std::vector<uint32_t> material_id_;
