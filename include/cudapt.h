@@ -99,6 +99,9 @@ typedef struct cudapt_stats {
   uint32_t n_spheres;
   double last_trace_ms;      /* CUDA-event time of the closest-hit BVH traversal launches inside the most
                                 recent cudapt_render() (mesh integrator; 0 for the sphere megakernel) */
+  uint64_t packet_nodes;     /* camera-ray packets (32 samples of a pixel, csrc/primary_packet.cu): node steps,   */
+  uint64_t packet_tris;      /* triangle steps (each tests 32 rays) and packets handed to the per-ray kernel --   */
+  uint64_t packet_bails;     /* only while counting, like nodes_visited                                            */
 } cudapt_stats;
 
 /* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */

@@ -51,6 +51,7 @@ class Stats(ctypes.Structure):
         ("accel_build_ms", ctypes.c_double), ("accel_bytes", ctypes.c_uint64), ("frame_count", ctypes.c_uint32),
         ("n_triangles", ctypes.c_uint32), ("n_nodes", ctypes.c_uint32), ("n_spheres", ctypes.c_uint32),
         ("last_trace_ms", ctypes.c_double),
+        ("packet_nodes", ctypes.c_uint64), ("packet_tris", ctypes.c_uint64), ("packet_bails", ctypes.c_uint64),
     ]
 
 

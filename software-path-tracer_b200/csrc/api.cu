@@ -622,6 +622,9 @@ int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out) {
   out->rays = c[kCntRays];
   out->nodes_visited = c[kCntNodes];
   out->tris_tested = c[kCntTris];
+  out->packet_nodes = c[kCntPacketNodes];
+  out->packet_tris = c[kCntPacketTris];
+  out->packet_bails = c[kCntPacketBail];
   out->shade_invocations = c[kCntShades];
   out->kernel_launches = ctx->launches;
   out->render_ms = ctx->render_ms;

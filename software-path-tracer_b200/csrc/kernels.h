@@ -10,6 +10,9 @@ enum CounterSlot : int {
   kCntPaths = 2,
   kCntNodes = 3,
   kCntTris = 4,
+  kCntPacketNodes = 5,  // primary_packet.cu: node / triangle steps per PACKET, packets handed to the per-ray kernel
+  kCntPacketTris = 6,
+  kCntPacketBail = 7,
   kCntSlots = 8
 };
 
@@ -88,6 +91,7 @@ struct PassParams {
   IntegratorParams ip;
   uint32_t n_pixels;
   uint32_t samples;          // samples of every pixel in this pass
+  uint32_t chunked;          // path id layout, see path_id()
   uint32_t first_frame;      // global 1-based frame index of sample 0 of this pass
   uint32_t frame_stride;
   float4* accum;
@@ -96,6 +100,23 @@ struct PassParams {
   unsigned long long* counters;  // global stats (CounterSlot)
 };
 
+// PATH ID of (pixel, sample-in-pass).  Sample-major (id = s * n_pixels + pixel: a warp of consecutive ids = 32
+// neighbouring pixels) or, when the camera rays are traced as packets (primary_packet.cu: one warp = 32 samples of a
+// pixel), CHUNKED: id = ((s / 32) * n_pixels + pixel) * 32 + s % 32, so that a packet's state is contiguous.
+__host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
+  return p.chunked ? (((s >> 5) * p.n_pixels + pixel) << 5) | (s & 31u) : s * p.n_pixels + pixel;
+}
+__host__ __device__ inline void path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
+  if (p.chunked) {
+    const uint32_t g = id >> 5, chunk = g / p.n_pixels;
+    pixel = g - chunk * p.n_pixels;
+    s = (chunk << 5) | (id & 31u);
+  } else {
+    s = id / p.n_pixels;
+    pixel = id - s * p.n_pixels;
+  }
+}
+
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = 8;
 constexpr int kShadeBlock = 256;
@@ -103,6 +124,13 @@ constexpr int kShadeBlocksPerSM = 4;
 
 cudaError_t launch_raygen(const PassParams& p, int sm_count, cudaStream_t s);
 cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue_in, bool counting, int sm_count, cudaStream_t s);
+// closest hit for an explicit queue of path ids (the packets' fall-back rays)
+cudaError_t launch_trace_queue(const PassParams& p, const uint32_t* queue, uint32_t* count, uint32_t* work, bool counting, int sm_count,
+                               cudaStream_t s);
+// primary_packet.cu: fused raygen + packet traversal of the camera rays of a pass
+bool primary_packets_enabled(const PassParams& p);
+cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
+                                   cudaStream_t s);
 cudaError_t launch_shade(const PassParams& p, uint32_t bounce, int queue_in, int sm_count, cudaStream_t s);
 cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool counting, int sm_count, cudaStream_t s);
 cudaError_t launch_accumulate(const PassParams& p, int sm_count, cudaStream_t s);

@@ -335,14 +335,28 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     p.aov_prim = done == 0 ? a.aov_prim : nullptr;
     p.aov_t = done == 0 ? a.aov_t : nullptr;
     R_TRY(cudaMemsetAsync(p.st.counters, 0, sizeof(uint32_t) * 4 * (size_t)(max_b + 2), stream), "counter memset");
-    R_TRY(launch_raygen(p, sm_count, stream), "raygen");
+    // camera rays: packets (one warp = 32 samples of a pixel; fused raygen) + the per-ray kernel for the rays of
+    // packets that gave up, or -- pass size not a multiple of 32 -- raygen + the per-ray kernel
+    p.chunked = 0;
+    const bool packets = primary_packets_enabled(p);
+    p.chunked = packets ? 1u : 0u;
+    uint32_t* fb = p.st.counters + 4 * (size_t)(max_b + 1);  // {fall-back count, fall-back work counter}
+    if (packets) {
+      R_TRY(launch_primary_packets(p, p.st.queue[1], fb, a.counting, sm_count, stream), "primary_packets");
+    } else {
+      R_TRY(launch_raygen(p, sm_count, stream), "raygen");
+    }
     ++*launches;
     for (uint32_t b = 0; b < max_b; ++b) {
       const int qin = (int)(b & 1u);
       cudaEvent_t e0 = nullptr, e1 = nullptr;
       next_trace_events(&e0, &e1);  // per-launch timing of the dominant kernel (bench.py roofline)
       if (e0) cudaEventRecord(e0, stream);
-      R_TRY(launch_trace_closest(p, b, qin, a.counting, sm_count, stream), "trace_closest");
+      if (b == 0 && packets) {
+        R_TRY(launch_trace_queue(p, p.st.queue[1], fb, fb + 1, a.counting, sm_count, stream), "trace_fallback");
+      } else {
+        R_TRY(launch_trace_closest(p, b, qin, a.counting, sm_count, stream), "trace_closest");
+      }
       if (e1) cudaEventRecord(e1, stream);
       R_TRY(launch_shade(p, b, qin, sm_count, stream), "shade");
       *launches += 2;

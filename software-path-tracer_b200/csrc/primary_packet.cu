@@ -1,0 +1,295 @@
+// K1+K2a: camera rays as PACKETS.  One warp = 32 samples of ONE pixel (a pinhole camera: common origin, directions
+// inside one pixel's footprint).  The warp generates the 32 rays (fused raygen: CPT.cpp:53-73 + jitter), walks the
+// BVH8 ONCE for all of them with a warp-uniform stack, and tests every candidate triangle with all 32 lanes.
+//
+// Why: the per-ray kernel (trace_bvh.cu) is alu-pipe bound on the 8-box node test (~210 instructions per lane and
+// node) and runs its triangle tests at 3-4 of 32 lanes (profiles/r01_notes.md).  Here the node test is SPLIT over
+// the warp -- lane = (child slot c, frustum plane pl): 3 byte conversions + 1 plane evaluation per lane, one ballot
+// -- and a triangle test occupies all 32 lanes.
+//
+// Exactness: the per-ray result is "smallest t >= tnear over all triangles, ties to the smallest caller index",
+// evaluated by the SAME tri_test() as the per-ray kernel and the CPU twin; it does not depend on which superset of
+// the ray's own candidates was tested.  The packet only has to be conservative: the four bounding planes of the
+// 32 directions are fattened by 1e-5 (relative), children are culled in depth only against the farthest current hit
+// of the packet (x 1.00001).  Rays of packets that stop paying off (budget of node + triangle steps, e.g. distant
+// geometry much smaller than a pixel) are handed to the per-ray kernel through a fall-back queue.
+#include <cstdlib>
+
+#include "bvh8_traverse.cuh"
+#include "kernels.h"
+
+namespace cudapt {
+namespace {
+
+constexpr int kPacketBlock = 128;
+constexpr int kPacketWarps = kPacketBlock / 32;
+constexpr int kPacketBlocksPerSM = 12;
+constexpr unsigned kFull = 0xffffffffu;
+
+__device__ __forceinline__ float sel3(f3 v, int ax) { return ax == 0 ? v.x : (ax == 1 ? v.y : v.z); }
+
+// order-preserving float <-> uint key (any sign), for the integer warp reductions
+__device__ __forceinline__ uint32_t fkey(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float funkey(uint32_t k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k); }
+
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 lds_u128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+struct PacketArgs {
+  PassParams p;
+  uint32_t* fb_queue;   // rays handed to the per-ray kernel
+  uint32_t* fb_count;
+  int axis_k;           // dominant axis of the camera's forward vector
+  float sigma;          // its sign
+  int budget;           // 3 per node step + 4 per triangle step
+};
+
+constexpr uint32_t kNodeBytes = 96;            // staged node: 80 B, padded
+constexpr uint32_t kTriSlots = 24;             // a node has at most 24 triangles
+constexpr uint32_t kWarpSmem = kNodeBytes + kTriSlots * 48u;
+
+template <bool kCount>
+__global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_packet_kernel(const PacketArgs a) {
+  __shared__ __align__(16) unsigned char s_warp[kPacketWarps * kWarpSmem];
+  __shared__ uint8_t s_lut[8 * 256];
+  for (int i = threadIdx.x; i < 8 * 256; i += kPacketBlock) s_lut[i] = (uint8_t)xor_permute8((uint32_t)i & 0xFFu, (uint32_t)i >> 8);
+  __syncthreads();
+  const PassParams& p = a.p;
+  const unsigned lane = threadIdx.x & 31u;
+  const uint32_t n_warps = gridDim.x * kPacketWarps;
+  const uint32_t n_tasks = p.n_pixels * (p.samples / 32u);
+  const int ax_k = a.axis_k, ax_a = (ax_k + 1) % 3, ax_b = (ax_k + 2) % 3;
+  const float sigma = a.sigma;
+  const f3 O = p.cam.origin;
+  const float O_k = sel3(O, ax_k);
+  // this warp's staging area: one node (20 words) + the candidate triangles of that node
+  const uint32_t sm_node = (uint32_t)__cvta_generic_to_shared(s_warp) + (threadIdx.x >> 5) * kWarpSmem;
+  const uint32_t sm_tris = sm_node + kNodeBytes;
+  const uint32_t sm_lut = (uint32_t)__cvta_generic_to_shared(s_lut);
+  // lane roles in the node test: child slot c, plane pl (0: u >= umin, 1: u <= umax, 2: v >= vmin, 3: v <= vmax)
+  const uint32_t c = lane & 7u, pl = lane >> 3;
+  const int ax_sel = pl < 2u ? ax_a : ax_b;
+  const float ca = (pl & 1u) ? -1.0f : 1.0f;
+  const float O_sel = sel3(O, ax_sel);
+  const uint32_t a_p_sel = sm_node + 4u * (uint32_t)ax_sel, a_e_sel = sm_node + 12u + (uint32_t)ax_sel;
+  const uint32_t a_q_sel = sm_node + ((pl & 1u) ? 32u : 56u) + 8u * (uint32_t)ax_sel + c;  // +1: far corner = hi; -1: lo
+  const uint32_t a_p_k = sm_node + 4u * (uint32_t)ax_k, a_e_k = sm_node + 12u + (uint32_t)ax_k;
+  const uint32_t a_q_k = sm_node + 32u + 8u * (uint32_t)ax_k + c;  // lo; hi is 24 bytes on
+  const uint32_t* node_words = reinterpret_cast<const uint32_t*>(p.scene.nodes) + (lane < 20u ? lane : 0u);
+
+  uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0;
+
+  for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) {
+    const uint32_t chunk = task / p.n_pixels, pixel = task - chunk * p.n_pixels;
+    const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
+    if (!owns_pixel(p.im, x, y)) continue;  // warp-uniform
+    // ---- the 32 rays (K1) ----
+    const uint32_t s = chunk * 32u + lane;
+    const uint32_t id = task * 32u + lane;  // chunked path id (kernels.h path_id())
+    const uint32_t frame = p.first_frame + s * p.frame_stride;
+    float jx = 0.0f, jy = 0.0f;
+    if (p.ip.jitter) {
+      const rand4 j = philox_block(pixel, frame, 0u, 2u, p.ip.seed);
+      jx = j.u0, jy = j.u1;
+    }
+    RayPre r;
+    r.o = O;
+    r.d = primary_dir(p.cam, p.im, x, y, jx, jy);
+    p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);
+    p.st.ray_d[id] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0x7f800000));
+    if (p.im.part_world <= 1u) {
+      p.st.queue[0][id] = id;
+    } else {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
+      base = __shfl_sync(kFull, base, 0);
+      p.st.queue[0][base + lane] = id;
+    }
+    // ---- bounding planes of the 32 directions ----
+    const float w = sigma * sel3(r.d, ax_k);  // depth per unit t
+    bool bail = __any_sync(kFull, !(w > 0.02f));
+    const float inv_w = 1.0f / w;
+    const float u = sel3(r.d, ax_a) * inv_w, v = sel3(r.d, ax_b) * inv_w;
+    // lanes of planes 0/1 reduce u, lanes of planes 2/3 reduce v; min for even planes, max for odd ones:
+    // every lane needs ONE of the four limits
+    const uint32_t ku = fkey(u), kv = fkey(v);
+    const uint32_t kumin = __reduce_min_sync(kFull, ku), kumax = __reduce_max_sync(kFull, ku);
+    const uint32_t kvmin = __reduce_min_sync(kFull, kv), kvmax = __reduce_max_sync(kFull, kv);
+    const float e0 = funkey(pl < 2u ? kumin : kvmin), e1 = funkey(pl < 2u ? kumax : kvmax);
+    const float dl = 1e-5f * (1.0f + fmaxf(fabsf(e0), fabsf(e1)));
+    // plane of this lane: ca * D_sel + ck * D_k >= 0, D = far corner of the child box along (ca, ck) minus the origin
+    const float lim = (pl & 1u) ? e1 + dl : e0 - dl;
+    const float ck = (ca > 0.0f ? -lim : lim) * sigma;
+    const uint32_t a_q_kp = a_q_k + (ck > 0.0f ? 24u : 0u);  // the k bound this lane's plane uses
+    const uint32_t octinv = 7u ^ ((r.d.x < 0.f ? 1u : 0u) | (r.d.y < 0.f ? 2u : 0u) | (r.d.z < 0.f ? 4u : 0u));
+    const uint32_t oct = __shfl_sync(kFull, octinv, 0);
+    const uint32_t a_lut = sm_lut + oct * 256u;
+
+    TraceHit hit;
+    hit.t = __int_as_float(0x7f800000);
+    hit.tri = 0xFFFFFFFFu;
+    hit.prim = 0xFFFFFFFFu;
+    float kmax = __int_as_float(0x7f800000);
+    uint2 ngroup = make_uint2(0u, 0x80000000u), sreg = make_uint2(0u, 0u);
+    int sp = 0, cost = 0;
+
+    while (!bail) {
+      // ---- node step (warp-uniform control) ----
+      const int bit = 31 - __clz(ngroup.y);
+      ngroup.y &= ~(1u << bit);
+      if (ngroup.y > 0x00FFFFFFu) {
+        if (sp == 32) {
+          bail = true;
+          break;
+        }
+        if ((int)lane == sp) sreg = ngroup;
+        ++sp;
+      }
+      const uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
+      const uint32_t rel = (uint32_t)__popc((ngroup.y & 0xFFu) & ~(0xFFFFFFFFu << slot));
+      const uint32_t node = ngroup.x + rel;
+      // stage the 80-byte node through shared memory: ONE coalesced load, then every lane picks its bytes
+      const uint32_t word = __ldg(node_words + 20u * (size_t)node);
+      __syncwarp();
+      if (lane < 20u) sts_u32(sm_node + 4u * lane, word);
+      __syncwarp();
+      const uint4 w1 = lds_u128(sm_node + 16u);
+      const float p_sel = __uint_as_float(lds_u32(a_p_sel)), p_k = __uint_as_float(lds_u32(a_p_k));
+      const uint32_t e_sel = lds_u8(a_e_sel), e_k = lds_u8(a_e_k), node_imask = lds_u8(sm_node + 15u);
+      const uint32_t q_sel = lds_u8(a_q_sel), q_klo = lds_u8(a_q_k), q_khi = lds_u8(a_q_k + 24u), q_kp = lds_u8(a_q_kp);
+      const float s_sel = __uint_as_float(e_sel << 23), s_k = __uint_as_float(e_k << 23);
+      const float D_sel = fmaf((float)q_sel, s_sel, p_sel - O_sel);
+      const float bk = p_k - O_k;
+      const float D_lo = fmaf((float)q_klo, s_k, bk), D_hi = fmaf((float)q_khi, s_k, bk), D_kp = fmaf((float)q_kp, s_k, bk);
+      const float val = fmaf(ck, D_kp, ca * D_sel);
+      const float n1 = sigma * D_lo, n2 = sigma * D_hi;
+      const bool ok = val >= 0.0f && fminf(n1, n2) <= kmax && fmaxf(n1, n2) >= 0.0f;
+      const unsigned bal = __ballot_sync(kFull, ok);
+      const uint32_t hits = bal & (bal >> 8) & (bal >> 16) & (bal >> 24) & 0xFFu;
+      const uint32_t prio = lds_u8(a_lut + (hits & node_imask));
+      ngroup = make_uint2(w1.x, (prio << 24) | node_imask);
+      const uint32_t tri_base = w1.y, tri_valid = w1.z;
+      uint32_t tmask = (hits * 0x010101u) & tri_valid;
+      cost += 3;
+      if (kCount) ++n_nodes;
+      // ---- every candidate triangle against all 32 rays ----
+      if (tmask) {
+        // lane b fetches candidate b (if any) into slot popc(lower candidates): all fetches of the node in flight together
+        if ((tmask >> lane) & 1u) {
+          const uint32_t below = (1u << lane) - 1u;
+          const float4* tp = p.scene.tris + 3 * (size_t)(tri_base + (uint32_t)__popc(tri_valid & below));
+          const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
+          const uint32_t dst = sm_tris + 48u * (uint32_t)__popc(tmask & below);
+          sts_u128(dst, *reinterpret_cast<const uint4*>(&ta));
+          sts_u128(dst + 16u, *reinterpret_cast<const uint4*>(&tb));
+          sts_u128(dst + 32u, *reinterpret_cast<const uint4*>(&tc));
+        }
+        __syncwarp();
+        uint32_t src = sm_tris;
+        do {
+          const uint32_t low = tmask & (0u - tmask);
+          tmask ^= low;
+          const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & (low - 1u));
+          const uint4 ua = lds_u128(src), ub = lds_u128(src + 16u), uc = lds_u128(src + 32u);
+          src += 48u;
+          float t;
+          if (tri_test(mk3(__uint_as_float(ua.x), __uint_as_float(ua.y), __uint_as_float(ua.z)),
+                       mk3(__uint_as_float(ub.x), __uint_as_float(ub.y), __uint_as_float(ub.z)),
+                       mk3(__uint_as_float(uc.x), __uint_as_float(uc.y), __uint_as_float(uc.z)), r.o, r.d, t) &&
+              t >= p.ip.tnear && (t < hit.t || (t == hit.t && ua.w < hit.prim))) {  // tri_step<false>'s closest-hit rule
+            hit.t = t;
+            hit.tri = tri;
+            hit.prim = ua.w;
+          }
+          cost += 4;
+          if (kCount) ++n_tris;
+        } while (tmask);
+        kmax = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(hit.t * w))) * 1.00001f;
+      }
+      if (ngroup.y <= 0x00FFFFFFu) {
+        if (sp == 0) break;
+        --sp;
+        ngroup.x = __shfl_sync(kFull, sreg.x, sp);
+        ngroup.y = __shfl_sync(kFull, sreg.y, sp);
+      }
+      if (cost > a.budget) bail = true;
+    }
+    if (!bail) {
+      p.st.hit[id] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
+      done_rays += 1u;
+    } else {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(a.fb_count, 32u);
+      base = __shfl_sync(kFull, base, 0);
+      a.fb_queue[base + lane] = id;
+      if (kCount) ++n_bail;
+    }
+  }
+  if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_pixels * p.samples;
+  const uint64_t wr = warp_sum_u32(done_rays);
+  if (lane == 0 && wr) atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
+  if (kCount && lane == 0) {
+    atomicAdd(&p.counters[kCntPacketNodes], (unsigned long long)n_nodes);
+    atomicAdd(&p.counters[kCntPacketTris], (unsigned long long)n_tris);
+    atomicAdd(&p.counters[kCntPacketBail], (unsigned long long)n_bail);
+  }
+}
+
+}  // namespace
+
+// Packets apply to a pass whose sample count is a multiple of 32 (one warp = 32 samples of one pixel);
+// CUDAPT_PRIMARY_PACKETS=0 switches them off.
+bool primary_packets_enabled(const PassParams& p) {
+  const char* e = getenv("CUDAPT_PRIMARY_PACKETS");  // read per pass: tests toggle it
+  const int on = e ? atoi(e) : 1;
+  return on != 0 && p.samples >= 32u && p.samples % 32u == 0u;
+}
+
+cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
+                                   cudaStream_t s) {
+  const char* be = getenv("CUDAPT_PACKET_BUDGET");
+  const int budget = be ? (atoi(be) < 0 ? 0 : atoi(be)) : 160;
+  PacketArgs a;
+  a.p = p;
+  a.fb_queue = fb_queue;
+  a.fb_count = fb_count;
+  const float f[3] = {p.cam.forward.x, p.cam.forward.y, p.cam.forward.z};
+  int k = 0;
+  for (int i = 1; i < 3; ++i)
+    if (fabsf(f[i]) > fabsf(f[k])) k = i;
+  a.axis_k = k;
+  a.sigma = f[k] < 0.0f ? -1.0f : 1.0f;
+  a.budget = budget;
+  const uint32_t n_tasks = p.n_pixels * (p.samples / 32u);
+  const uint32_t warps_per_cta = kPacketWarps;
+  uint32_t grid = (uint32_t)sm_count * kPacketBlocksPerSM;
+  const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;
+  if (need < grid) grid = need ? need : 1u;
+  if (counting)
+    primary_packet_kernel<true><<<grid, kPacketBlock, 0, s>>>(a);
+  else
+    primary_packet_kernel<false><<<grid, kPacketBlock, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace cudapt

@@ -255,6 +255,12 @@ cudaError_t launch_trace_closest(const PassParams& p, uint32_t bounce, int queue
                              st.counters + slot_trace_work(bounce), st.hit, nullptr, nullptr, counting, sm_count, s);
 }
 
+cudaError_t launch_trace_queue(const PassParams& p, const uint32_t* queue, uint32_t* count, uint32_t* work, bool counting, int sm_count,
+                               cudaStream_t s) {
+  const WavefrontState& st = p.st;
+  return launch_trace<false>(p, st.ray_o, st.ray_d, queue, count, work, st.hit, nullptr, nullptr, counting, sm_count, s);
+}
+
 cudaError_t launch_trace_shadow(const PassParams& p, uint32_t bounce, bool counting, int sm_count, cudaStream_t s) {
   const WavefrontState& st = p.st;
   return launch_trace<true>(p, st.sh_o, st.sh_d, st.shadow_queue, st.counters + slot_shadow_count(bounce),

@@ -157,8 +157,8 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
     path_2 = (k + 2 < rounds && i + 2 * stride < n) ? qin[i + 2 * stride] : 0u;
     if (k + 1 < rounds) hit_1 = st.hit[path_1];  // path_1 was loaded a round ago: no stall here
     if (i < n) {
-      const uint32_t s = path / p.n_pixels;
-      const uint32_t pixel = path - s * p.n_pixels;
+      uint32_t s, pixel;
+      path_decode(p, path, pixel, s);
       const uint32_t frame = p.first_frame + s * p.frame_stride;
       const float t = __uint_as_float(h.x);
       const float4 o4 = st.ray_o[path], d4 = st.ray_d[path];
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(kShadeBlock) accumulate_kernel(const PassParam
     if (!owns_pixel(p.im, x, y)) continue;
     float4 acc = p.accum[pixel];
     for (uint32_t s = 0; s < p.samples; ++s) {
-      const float4 l = p.st.L[(size_t)s * p.n_pixels + pixel];
+      const float4 l = p.st.L[path_id(p, pixel, s)];
       acc.x += l.x;
       acc.y += l.y;
       acc.z += l.z;
