@@ -301,7 +301,12 @@ def main():
         tr.set_counting(True)
         tr.render(min(spp, int(wl["cfg"].get("samples_per_pass", 1))))
         cs = tr.stats()
-        tr._counted = {"nodes_per_ray": cs.nodes_visited / max(cs.rays, 1), "tris_per_ray": cs.tris_tested / max(cs.rays, 1)}
+        # nodes_visited / tris_tested are counted by the per-ray kernel only: closest-hit rays it traced + shadow rays
+        per_ray = max(cs.rays - cs.packet_rays, 1)
+        n_pk = max(cs.packet_rays // 32 + cs.packet_bails, 1)
+        tr._counted = {"nodes_per_ray": cs.nodes_visited / per_ray, "tris_per_ray": cs.tris_tested / per_ray,
+                       "packet_nodes": cs.packet_nodes / n_pk, "packet_tris": cs.packet_tris / n_pk,
+                       "packet_bail_frac": cs.packet_bails / n_pk if cs.packet_rays or cs.packet_bails else None}
         tr.set_counting(False)
     for _ in range(args.warmup):
         step()
@@ -449,31 +454,46 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
     if Nn is None:
         return {"bound": "hbm", "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None, "traffic": None,
                 "peak_source": peak_src, "note": "node/triangle counters unavailable"}
-    bytes_per_path = R * (Nn * 80.0 + Nt * 48.0) + B * 160.0 + 32.0
-    # Dominant kernel = trace_kernel (closest-hit BVH traversal).  Its launches of the last render are timed
+    # Dominant kernel = trace_kernel<closest> (per-ray BVH traversal).  Its launches of the last render are timed
     # inside libcudapt with CUDA-event pairs on the launch stream (stats.last_trace_ms = their sum).
     # Algorithmic bytes of those launches: per ray 36 B in (ray + queue id) + 8 B out (hit) + Nn nodes x 80 B
-    # + Nt triangles x 48 B.  Reported per launch: both divided by the number of trace launches.
+    # + Nt triangles x 48 B, over the closest-hit rays the kernel traced = all rays - shadow rays - camera rays
+    # finished by packets (primary_packet.cu).  Reported per launch: both divided by the number of trace launches.
     rays = float(st.rays)
+    closest_rays = float(st.rays - st.shadow_rays - st.packet_rays)
+    per_ray_rays = float(st.rays - st.packet_rays)
+    n_packets = st.packet_rays / 32.0
+    pk_bytes = n_packets * (counted["packet_nodes"] * 80.0 + counted["packet_tris"] * 48.0 + 32 * 44.0)
+    bytes_per_path = (per_ray_rays * (Nn * 80.0 + Nt * 48.0) + pk_bytes) / paths + B * 160.0 + 32.0
     trace_ms = float(st.last_trace_ms)
     n_launches = max(1, -(-spp // int(wl["cfg"].get("samples_per_pass", 1))) * int(wl["cfg"].get("max_bounces", 4)))
-    trace_bytes = rays * (44.0 + Nn * 80.0 + Nt * 48.0)
+    trace_bytes = closest_rays * (44.0 + Nn * 80.0 + Nt * 48.0)
     achieved = trace_bytes / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else None
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "trace_dram_traffic.json")
     if os.path.exists(tpath):
         t = json.load(open(tpath)).get(wl["name"])
         if t:
-            traffic = t["dram_bytes_per_ray"] * rays / n_launches
+            traffic = t["dram_bytes_per_ray"] * closest_rays / n_launches
+    packets = None
+    if st.packet_rays:
+        packets = {"kernel": "primary_packet_kernel", "share_of_step": st.last_packet_ms / render_ms if render_ms else None,
+                   "ms_per_step": st.last_packet_ms, "camera_rays_finished": int(st.packet_rays),
+                   "node_steps_per_packet": counted["packet_nodes"], "triangle_steps_per_packet": counted["packet_tris"],
+                   "handed_to_per_ray_kernel": counted["packet_bail_frac"],
+                   "algorithmic_GBps": pk_bytes / (st.last_packet_ms * 1e-3) / 1e9 if st.last_packet_ms else None,
+                   "note": "one warp = 32 samples of a pixel: fused ray generation + shared BVH walk; issue bound "
+                           "(profiles/r01_notes.md), bytes given for completeness"}
     return {"bound": "hbm", "kernel": "trace_kernel<closest>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
             "frac": achieved / hbm_peak if achieved else None, "traffic": traffic,
             "algorithmic_bytes_per_launch": trace_bytes / n_launches, "launch_ms": trace_ms / n_launches,
             "launches_per_step": n_launches, "kernel_share_of_step": trace_ms / render_ms if render_ms else None,
             "peak_source": peak_src, "bytes_per_ray": 44.0 + Nn * 80.0 + Nt * 48.0, "bytes_per_path_whole_step": bytes_per_path,
             "whole_step_GBps": bytes_per_path * n_px * spp / (render_ms * 1e-3) / 1e9,
-            "R": R, "Nn": Nn, "Nt": Nt, "B": B,
-            "note": "BVH of c2/c3 is L2-resident, so DRAM traffic is far below the algorithmic bytes and the kernel is "
-                    "issue/latency bound (profiles/r01_notes.md); c4 (1.3 GB BVH) is the HBM-gather case"}
+            "R": R, "Nn": Nn, "Nt": Nt, "B": B, "rays_traced_by_this_kernel_per_step": closest_rays, "packets": packets,
+            "note": "Nn/Nt: nodes / triangles per ray of the per-ray kernel (camera rays finished by packets excluded). "
+                    "BVH of c2/c3 is L2-resident, so DRAM traffic is far below the algorithmic bytes and the kernel is "
+                    "issue bound (profiles/r01_notes.md); c4 (1.3 GB BVH) is the HBM-gather case"}
 
 
 if __name__ == "__main__":

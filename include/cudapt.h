@@ -102,6 +102,9 @@ typedef struct cudapt_stats {
   uint64_t packet_nodes;     /* camera-ray packets (32 samples of a pixel, csrc/primary_packet.cu): node steps,   */
   uint64_t packet_tris;      /* triangle steps (each tests 32 rays) and packets handed to the per-ray kernel --   */
   uint64_t packet_bails;     /* only while counting, like nodes_visited                                            */
+  uint64_t packet_rays;      /* camera rays finished by packets (part of .rays; always counted)                    */
+  uint64_t shadow_rays;      /* any-hit queries (part of .rays; always counted)                                    */
+  double last_packet_ms;     /* CUDA-event time of the packet launches inside the most recent cudapt_render()      */
 } cudapt_stats;
 
 /* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */

@@ -52,6 +52,7 @@ class Stats(ctypes.Structure):
         ("n_triangles", ctypes.c_uint32), ("n_nodes", ctypes.c_uint32), ("n_spheres", ctypes.c_uint32),
         ("last_trace_ms", ctypes.c_double),
         ("packet_nodes", ctypes.c_uint64), ("packet_tris", ctypes.c_uint64), ("packet_bails", ctypes.c_uint64),
+        ("packet_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64), ("last_packet_ms", ctypes.c_double),
     ]
 
 

@@ -58,7 +58,7 @@ struct cudapt_ctx {
 
   // stats
   uint64_t launches = 0;
-  double render_ms = 0.0, last_render_ms = 0.0, last_trace_ms = 0.0;
+  double render_ms = 0.0, last_render_ms = 0.0, last_trace_ms = 0.0, last_packet_ms = 0.0;
   bool timing_pending = false;
 };
 
@@ -146,6 +146,7 @@ int finish_timing(cudapt_ctx* ctx) {
   CU_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->last_render_ms = ms;
   ctx->last_trace_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_trace_ms() : 0.0;
+  ctx->last_packet_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_packet_ms() : 0.0;
   ctx->render_ms += ms;
   ctx->timing_pending = false;
   return CUDAPT_OK;
@@ -625,6 +626,9 @@ int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out) {
   out->packet_nodes = c[kCntPacketNodes];
   out->packet_tris = c[kCntPacketTris];
   out->packet_bails = c[kCntPacketBail];
+  out->packet_rays = c[kCntPacketRays];
+  out->shadow_rays = c[kCntShadowRays];
+  out->last_packet_ms = ctx->last_packet_ms;
   out->shade_invocations = c[kCntShades];
   out->kernel_launches = ctx->launches;
   out->render_ms = ctx->render_ms;

@@ -13,7 +13,9 @@ enum CounterSlot : int {
   kCntPacketNodes = 5,  // primary_packet.cu: node / triangle steps per PACKET, packets handed to the per-ray kernel
   kCntPacketTris = 6,
   kCntPacketBail = 7,
-  kCntSlots = 8
+  kCntPacketRays = 8,   // camera rays finished by packets (always counted; also included in kCntRays)
+  kCntShadowRays = 9,   // any-hit queries (always counted; also included in kCntRays)
+  kCntSlots = 12
 };
 
 constexpr int kSphereBlockX = 16;

@@ -75,6 +75,9 @@ void MeshScene::release() {
   for (cudaEvent_t e : trace_events_) cudaEventDestroy(e);
   trace_events_.clear();
   trace_events_used_ = 0;
+  for (cudaEvent_t e : packet_events_) cudaEventDestroy(e);
+  packet_events_.clear();
+  packet_events_used_ = 0;
   if (dev_) {
     dev_->free_state();
     dev_->free_scene();
@@ -244,6 +247,15 @@ void MeshScene::next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1) {
   *e1 = trace_events_[trace_events_used_++];
 }
 
+double MeshScene::collect_packet_ms() {
+  double total = 0.0;
+  for (size_t i = 0; i + 1 < packet_events_used_; i += 2) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, packet_events_[i], packet_events_[i + 1]) == cudaSuccess) total += ms;
+  }
+  return total;
+}
+
 // Sum of the closest-hit traversal launches of the last render(); call after the stream has been synchronised.
 double MeshScene::collect_trace_ms() {
   double total = 0.0;
@@ -282,6 +294,7 @@ static cudaError_t ensure_state(MeshDevice* d, uint32_t paths, uint32_t bounces)
 cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err) {
   *launches = 0;
   trace_events_used_ = 0;
+  packet_events_used_ = 0;
   if (!dev_ || !dev_->d_nodes) {
     *err = "accel not built";
     return cudaErrorInvalidValue;
@@ -342,7 +355,21 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     p.chunked = packets ? 1u : 0u;
     uint32_t* fb = p.st.counters + 4 * (size_t)(max_b + 1);  // {fall-back count, fall-back work counter}
     if (packets) {
+      cudaEvent_t e0 = nullptr, e1 = nullptr;
+      if (packet_events_used_ + 2 <= 1024) {
+        while (packet_events_.size() < packet_events_used_ + 2) {
+          cudaEvent_t e;
+          if (cudaEventCreate(&e) != cudaSuccess) break;
+          packet_events_.push_back(e);
+        }
+        if (packet_events_.size() >= packet_events_used_ + 2) {
+          e0 = packet_events_[packet_events_used_++];
+          e1 = packet_events_[packet_events_used_++];
+        }
+      }
+      if (e0) cudaEventRecord(e0, stream);
       R_TRY(launch_primary_packets(p, p.st.queue[1], fb, a.counting, sm_count, stream), "primary_packets");
+      if (e1) cudaEventRecord(e1, stream);
     } else {
       R_TRY(launch_raygen(p, sm_count, stream), "raygen");
     }

@@ -49,6 +49,7 @@ class MeshScene {
   uint32_t n_nodes() const { return n_nodes_built_; }
   // CUDA-event time of the closest-hit traversal launches of the last render() (call after a stream sync).
   double collect_trace_ms();
+  double collect_packet_ms();
 
  private:
   bool refresh_staging(cudaStream_t stream, std::string* err);
@@ -61,6 +62,8 @@ class MeshScene {
   void next_trace_events(cudaEvent_t* e0, cudaEvent_t* e1);
   std::vector<cudaEvent_t> trace_events_;
   size_t trace_events_used_ = 0;
+  std::vector<cudaEvent_t> packet_events_;  // pairs around the camera-ray packet launches
+  size_t packet_events_used_ = 0;
 };
 
 }  // namespace cudapt

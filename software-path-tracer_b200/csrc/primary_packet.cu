@@ -23,7 +23,6 @@ namespace {
 
 constexpr int kPacketBlock = 128;
 constexpr int kPacketWarps = kPacketBlock / 32;
-constexpr int kPacketBlocksPerSM = 12;
 constexpr unsigned kFull = 0xffffffffu;
 
 __device__ __forceinline__ float sel3(f3 v, int ax) { return ax == 0 ? v.x : (ax == 1 ? v.y : v.z); }
@@ -55,6 +54,19 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// hides how a value was computed, so that the compiler keeps it in a register instead of recomputing it
+__device__ __forceinline__ uint32_t opaque(uint32_t v) {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
+}
+
+__device__ __forceinline__ const uint32_t* opaque_ptr(const uint32_t* v) {
+  const uint32_t* r;
+  asm volatile("mov.u64 %0, %1;" : "=l"(r) : "l"(v));
+  return r;
+}
+
 struct PacketArgs {
   PassParams p;
   uint32_t* fb_queue;   // rays handed to the per-ray kernel
@@ -64,12 +76,12 @@ struct PacketArgs {
   int budget;           // 3 per node step + 4 per triangle step
 };
 
-constexpr uint32_t kNodeBytes = 96;            // staged node: 80 B, padded
+constexpr uint32_t kNodeBytes = 96;            // staged node: 80 B + 3 scale words, padded
 constexpr uint32_t kTriSlots = 24;             // a node has at most 24 triangles
 constexpr uint32_t kWarpSmem = kNodeBytes + kTriSlots * 48u;
 
-template <bool kCount>
-__global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_packet_kernel(const PacketArgs a) {
+template <bool kCount, int kBlocksPerSM>
+__global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_kernel(const PacketArgs a) {
   __shared__ __align__(16) unsigned char s_warp[kPacketWarps * kWarpSmem];
   __shared__ uint8_t s_lut[8 * 256];
   for (int i = threadIdx.x; i < 8 * 256; i += kPacketBlock) s_lut[i] = (uint8_t)xor_permute8((uint32_t)i & 0xFFu, (uint32_t)i >> 8);
@@ -83,19 +95,28 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
   const f3 O = p.cam.origin;
   const float O_k = sel3(O, ax_k);
   // this warp's staging area: one node (20 words) + the candidate triangles of that node
-  const uint32_t sm_node = (uint32_t)__cvta_generic_to_shared(s_warp) + (threadIdx.x >> 5) * kWarpSmem;
-  const uint32_t sm_tris = sm_node + kNodeBytes;
+  uint32_t sm_node = (uint32_t)__cvta_generic_to_shared(s_warp) + (threadIdx.x >> 5) * kWarpSmem;
   const uint32_t sm_lut = (uint32_t)__cvta_generic_to_shared(s_lut);
   // lane roles in the node test: child slot c, plane pl (0: u >= umin, 1: u <= umax, 2: v >= vmin, 3: v <= vmax)
   const uint32_t c = lane & 7u, pl = lane >> 3;
   const int ax_sel = pl < 2u ? ax_a : ax_b;
   const float ca = (pl & 1u) ? -1.0f : 1.0f;
   const float O_sel = sel3(O, ax_sel);
-  const uint32_t a_p_sel = sm_node + 4u * (uint32_t)ax_sel, a_e_sel = sm_node + 12u + (uint32_t)ax_sel;
-  const uint32_t a_q_sel = sm_node + ((pl & 1u) ? 32u : 56u) + 8u * (uint32_t)ax_sel + c;  // +1: far corner = hi; -1: lo
-  const uint32_t a_p_k = sm_node + 4u * (uint32_t)ax_k, a_e_k = sm_node + 12u + (uint32_t)ax_k;
-  const uint32_t a_q_k = sm_node + 32u + 8u * (uint32_t)ax_k + c;  // lo; hi is 24 bytes on
-  const uint32_t* node_words = reinterpret_cast<const uint32_t*>(p.scene.nodes) + (lane < 20u ? lane : 0u);
+  // Staged node layout: words 0..19 = the node, words 20..22 = the three grid scales 2^(e-127) as floats (written by
+  // lanes 20..22 from their own copy of word 3), so that p and scale of an axis share one address register.
+  // The addresses go through opaque() once: ptxas otherwise re-derives them from %tid in every node step.
+  const uint32_t a_ax_sel = opaque(sm_node + 4u * (uint32_t)ax_sel);  // p at +0, scale at +80
+  const uint32_t a_ax_k = opaque(sm_node + 4u * (uint32_t)ax_k);
+  const uint32_t a_q_sel = opaque(sm_node + ((pl & 1u) ? 32u : 56u) + 8u * (uint32_t)ax_sel + c);  // +1: far corner = hi; -1: lo
+  const uint32_t a_q_k = opaque(sm_node + 32u + 8u * (uint32_t)ax_k + c);  // lo; hi is 24 bytes on
+  const uint32_t a_stage = opaque(sm_node + 4u * lane);
+  // staged value = prmt(word, 0, stage_sel) >> stage_shr: the word itself (lanes 0..19) or byte j of word 3 moved to
+  // the exponent field (lanes 20 + j)
+  const bool scale_lane = lane >= 20u && lane < 23u;
+  const uint32_t stage_sel = opaque(scale_lane ? ((lane - 20u) << 12) | 0x444u : 0x3210u);
+  const uint32_t stage_shr = opaque(scale_lane ? 1u : 0u);
+  const uint32_t* node_words = opaque_ptr(reinterpret_cast<const uint32_t*>(p.scene.nodes) + (lane < 20u ? lane : 3u));
+  sm_node = opaque(sm_node);
 
   uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0;
 
@@ -140,10 +161,10 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
     // plane of this lane: ca * D_sel + ck * D_k >= 0, D = far corner of the child box along (ca, ck) minus the origin
     const float lim = (pl & 1u) ? e1 + dl : e0 - dl;
     const float ck = (ca > 0.0f ? -lim : lim) * sigma;
-    const uint32_t a_q_kp = a_q_k + (ck > 0.0f ? 24u : 0u);  // the k bound this lane's plane uses
+    const uint32_t a_q_kp = opaque(a_q_k + (ck > 0.0f ? 24u : 0u));  // the k bound this lane's plane uses
     const uint32_t octinv = 7u ^ ((r.d.x < 0.f ? 1u : 0u) | (r.d.y < 0.f ? 2u : 0u) | (r.d.z < 0.f ? 4u : 0u));
     const uint32_t oct = __shfl_sync(kFull, octinv, 0);
-    const uint32_t a_lut = sm_lut + oct * 256u;
+    const uint32_t a_lut = opaque(sm_lut + oct * 256u);
 
     TraceHit hit;
     hit.t = __int_as_float(0x7f800000);
@@ -155,7 +176,7 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
 
     while (!bail) {
       // ---- node step (warp-uniform control) ----
-      const int bit = 31 - __clz(ngroup.y);
+      const int bit = pt_bfind(ngroup.y);
       ngroup.y &= ~(1u << bit);
       if (ngroup.y > 0x00FFFFFFu) {
         if (sp == 32) {
@@ -171,13 +192,13 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
       // stage the 80-byte node through shared memory: ONE coalesced load, then every lane picks its bytes
       const uint32_t word = __ldg(node_words + 20u * (size_t)node);
       __syncwarp();
-      if (lane < 20u) sts_u32(sm_node + 4u * lane, word);
+      if (lane < 23u) sts_u32(a_stage, __byte_perm(word, 0u, stage_sel) >> stage_shr);
       __syncwarp();
       const uint4 w1 = lds_u128(sm_node + 16u);
-      const float p_sel = __uint_as_float(lds_u32(a_p_sel)), p_k = __uint_as_float(lds_u32(a_p_k));
-      const uint32_t e_sel = lds_u8(a_e_sel), e_k = lds_u8(a_e_k), node_imask = lds_u8(sm_node + 15u);
+      const uint32_t node_imask = lds_u8(sm_node + 15u);
+      const float p_sel = __uint_as_float(lds_u32(a_ax_sel)), s_sel = __uint_as_float(lds_u32(a_ax_sel + 80u));
+      const float p_k = __uint_as_float(lds_u32(a_ax_k)), s_k = __uint_as_float(lds_u32(a_ax_k + 80u));
       const uint32_t q_sel = lds_u8(a_q_sel), q_klo = lds_u8(a_q_k), q_khi = lds_u8(a_q_k + 24u), q_kp = lds_u8(a_q_kp);
-      const float s_sel = __uint_as_float(e_sel << 23), s_k = __uint_as_float(e_k << 23);
       const float D_sel = fmaf((float)q_sel, s_sel, p_sel - O_sel);
       const float bk = p_k - O_k;
       const float D_lo = fmaf((float)q_klo, s_k, bk), D_hi = fmaf((float)q_khi, s_k, bk), D_kp = fmaf((float)q_kp, s_k, bk);
@@ -199,13 +220,13 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
           const uint32_t below = (1u << lane) - 1u;
           const float4* tp = p.scene.tris + 3 * (size_t)(tri_base + (uint32_t)__popc(tri_valid & below));
           const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
-          const uint32_t dst = sm_tris + 48u * (uint32_t)__popc(tmask & below);
+          const uint32_t dst = sm_node + kNodeBytes + 48u * (uint32_t)__popc(tmask & below);
           sts_u128(dst, *reinterpret_cast<const uint4*>(&ta));
           sts_u128(dst + 16u, *reinterpret_cast<const uint4*>(&tb));
           sts_u128(dst + 32u, *reinterpret_cast<const uint4*>(&tc));
         }
         __syncwarp();
-        uint32_t src = sm_tris;
+        uint32_t src = sm_node + kNodeBytes;
         do {
           const uint32_t low = tmask & (0u - tmask);
           tmask ^= low;
@@ -247,7 +268,10 @@ __global__ void __launch_bounds__(kPacketBlock, kPacketBlocksPerSM) primary_pack
   }
   if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_pixels * p.samples;
   const uint64_t wr = warp_sum_u32(done_rays);
-  if (lane == 0 && wr) atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
+  if (lane == 0 && wr) {
+    atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
+    atomicAdd(&p.counters[kCntPacketRays], (unsigned long long)wr);
+  }
   if (kCount && lane == 0) {
     atomicAdd(&p.counters[kCntPacketNodes], (unsigned long long)n_nodes);
     atomicAdd(&p.counters[kCntPacketTris], (unsigned long long)n_tris);
@@ -268,7 +292,7 @@ bool primary_packets_enabled(const PassParams& p) {
 cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
                                    cudaStream_t s) {
   const char* be = getenv("CUDAPT_PACKET_BUDGET");
-  const int budget = be ? (atoi(be) < 0 ? 0 : atoi(be)) : 160;
+  const int budget = be ? (atoi(be) < 0 ? 0 : atoi(be)) : 400;
   PacketArgs a;
   a.p = p;
   a.fb_queue = fb_queue;
@@ -282,13 +306,24 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
   a.budget = budget;
   const uint32_t n_tasks = p.n_pixels * (p.samples / 32u);
   const uint32_t warps_per_cta = kPacketWarps;
-  uint32_t grid = (uint32_t)sm_count * kPacketBlocksPerSM;
+  const char* ke = getenv("CUDAPT_PACKET_BLOCKS");  // register budget: CTAs per SM the kernel is compiled for
+  const int bps = ke ? atoi(ke) : 8;
+  uint32_t grid = (uint32_t)sm_count * (uint32_t)(bps == 12 ? 12 : (bps == 10 ? 10 : 8));
   const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;
   if (need < grid) grid = need ? need : 1u;
-  if (counting)
-    primary_packet_kernel<true><<<grid, kPacketBlock, 0, s>>>(a);
-  else
-    primary_packet_kernel<false><<<grid, kPacketBlock, 0, s>>>(a);
+#define PK_LAUNCH(B)                                                     \
+  if (counting)                                                          \
+    primary_packet_kernel<true, B><<<grid, kPacketBlock, 0, s>>>(a);     \
+  else                                                                   \
+    primary_packet_kernel<false, B><<<grid, kPacketBlock, 0, s>>>(a)
+  if (bps == 12) {
+    PK_LAUNCH(12);
+  } else if (bps == 10) {
+    PK_LAUNCH(10);
+  } else {
+    PK_LAUNCH(8);
+  }
+#undef PK_LAUNCH
   return cudaGetLastError();
 }
 

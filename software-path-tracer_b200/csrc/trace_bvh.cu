@@ -191,7 +191,10 @@ __global__ void __launch_bounds__(kTraceBlock, kBlocksPerSM)
       atomicAdd(&stats[kCntTris], (unsigned long long)wt);
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[kCntRays], (unsigned long long)n);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&stats[kCntRays], (unsigned long long)n);
+    if (kAnyHit) atomicAdd(&stats[kCntShadowRays], (unsigned long long)n);
+  }
 }
 
 
