@@ -80,8 +80,10 @@ constexpr uint32_t kNodeBytes = 96;            // staged node: 80 B + 3 scale wo
 constexpr uint32_t kTriSlots = 24;             // a node has at most 24 triangles
 constexpr uint32_t kWarpSmem = kNodeBytes + kTriSlots * 48u;
 
-template <bool kCount, int kBlocksPerSM>
-__global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_kernel(const PacketArgs a) {
+// kRays = rays per lane: a packet is 32 * kRays samples of one pixel (kRays consecutive 32-sample chunks), so the
+// node steps -- the larger part of a packet's cost -- are shared by more rays when the pass is deep enough.
+template <bool kCount, int kRays>
+__global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6 : 4)) primary_packet_kernel(const PacketArgs a) {
   __shared__ __align__(16) unsigned char s_warp[kPacketWarps * kWarpSmem];
   __shared__ uint8_t s_lut[8 * 256];
   for (int i = threadIdx.x; i < 8 * 256; i += kPacketBlock) s_lut[i] = (uint8_t)xor_permute8((uint32_t)i & 0xFFu, (uint32_t)i >> 8);
@@ -89,7 +91,7 @@ __global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_ker
   const PassParams& p = a.p;
   const unsigned lane = threadIdx.x & 31u;
   const uint32_t n_warps = gridDim.x * kPacketWarps;
-  const uint32_t n_tasks = p.n_pixels * (p.samples / 32u);
+  const uint32_t n_tasks = p.n_pixels * (p.samples / (32u * kRays));
   const int ax_k = a.axis_k, ax_a = (ax_k + 1) % 3, ax_b = (ax_k + 2) % 3;
   const float sigma = a.sigma;
   const f3 O = p.cam.origin;
@@ -124,52 +126,61 @@ __global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_ker
     const uint32_t chunk = task / p.n_pixels, pixel = task - chunk * p.n_pixels;
     const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
     if (!owns_pixel(p.im, x, y)) continue;  // warp-uniform
-    // ---- the 32 rays (K1) ----
-    const uint32_t s = chunk * 32u + lane;
-    const uint32_t id = task * 32u + lane;  // chunked path id (kernels.h path_id())
-    const uint32_t frame = p.first_frame + s * p.frame_stride;
-    float jx = 0.0f, jy = 0.0f;
-    if (p.ip.jitter) {
-      const rand4 j = philox_block(pixel, frame, 0u, 2u, p.ip.seed);
-      jx = j.u0, jy = j.u1;
+    // ---- the 32 * kRays rays (K1); ray j of a lane is sample 32 * (chunk * kRays + j) + lane ----
+    const uint32_t id0 = ((chunk * kRays) * p.n_pixels + pixel) * 32u + lane;  // chunked path id (kernels.h path_id())
+    const uint32_t id_step = p.n_pixels * 32u;                                 // to the same lane of the next chunk
+    f3 dir[kRays];
+    float w[kRays];  // depth per unit t
+    uint32_t ku_min = 0xFFFFFFFFu, ku_max = 0u, kv_min = 0xFFFFFFFFu, kv_max = 0u;
+    bool bail = false;
+#pragma unroll
+    for (int j = 0; j < kRays; ++j) {
+      const uint32_t s = (chunk * kRays + (uint32_t)j) * 32u + lane;
+      const uint32_t id = id0 + (uint32_t)j * id_step;
+      const uint32_t frame = p.first_frame + s * p.frame_stride;
+      float jx = 0.0f, jy = 0.0f;
+      if (p.ip.jitter) {
+        const rand4 jit = philox_block(pixel, frame, 0u, 2u, p.ip.seed);
+        jx = jit.u0, jy = jit.u1;
+      }
+      dir[j] = primary_dir(p.cam, p.im, x, y, jx, jy);
+      p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);
+      p.st.ray_d[id] = make_float4(dir[j].x, dir[j].y, dir[j].z, __int_as_float(0x7f800000));
+      if (p.im.part_world <= 1u) {
+        p.st.queue[0][id] = id;
+      } else {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
+        base = __shfl_sync(kFull, base, 0);
+        p.st.queue[0][base + lane] = id;
+      }
+      w[j] = sigma * sel3(dir[j], ax_k);
+      bail = bail || !(w[j] > 0.02f);
+      const float inv_w = 1.0f / w[j];
+      const uint32_t ku = fkey(sel3(dir[j], ax_a) * inv_w), kv = fkey(sel3(dir[j], ax_b) * inv_w);
+      ku_min = min(ku_min, ku), ku_max = max(ku_max, ku), kv_min = min(kv_min, kv), kv_max = max(kv_max, kv);
     }
-    RayPre r;
-    r.o = O;
-    r.d = primary_dir(p.cam, p.im, x, y, jx, jy);
-    p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);
-    p.st.ray_d[id] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0x7f800000));
-    if (p.im.part_world <= 1u) {
-      p.st.queue[0][id] = id;
-    } else {
-      uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
-      base = __shfl_sync(kFull, base, 0);
-      p.st.queue[0][base + lane] = id;
-    }
-    // ---- bounding planes of the 32 directions ----
-    const float w = sigma * sel3(r.d, ax_k);  // depth per unit t
-    bool bail = __any_sync(kFull, !(w > 0.02f));
-    const float inv_w = 1.0f / w;
-    const float u = sel3(r.d, ax_a) * inv_w, v = sel3(r.d, ax_b) * inv_w;
-    // lanes of planes 0/1 reduce u, lanes of planes 2/3 reduce v; min for even planes, max for odd ones:
-    // every lane needs ONE of the four limits
-    const uint32_t ku = fkey(u), kv = fkey(v);
-    const uint32_t kumin = __reduce_min_sync(kFull, ku), kumax = __reduce_max_sync(kFull, ku);
-    const uint32_t kvmin = __reduce_min_sync(kFull, kv), kvmax = __reduce_max_sync(kFull, kv);
+    bail = __any_sync(kFull, bail);
+    // ---- bounding planes of the directions: lanes of planes 0/1 need a u limit, lanes of planes 2/3 a v limit ----
+    const uint32_t kumin = __reduce_min_sync(kFull, ku_min), kumax = __reduce_max_sync(kFull, ku_max);
+    const uint32_t kvmin = __reduce_min_sync(kFull, kv_min), kvmax = __reduce_max_sync(kFull, kv_max);
     const float e0 = funkey(pl < 2u ? kumin : kvmin), e1 = funkey(pl < 2u ? kumax : kvmax);
     const float dl = 1e-5f * (1.0f + fmaxf(fabsf(e0), fabsf(e1)));
     // plane of this lane: ca * D_sel + ck * D_k >= 0, D = far corner of the child box along (ca, ck) minus the origin
     const float lim = (pl & 1u) ? e1 + dl : e0 - dl;
     const float ck = (ca > 0.0f ? -lim : lim) * sigma;
     const uint32_t a_q_kp = opaque(a_q_k + (ck > 0.0f ? 24u : 0u));  // the k bound this lane's plane uses
-    const uint32_t octinv = 7u ^ ((r.d.x < 0.f ? 1u : 0u) | (r.d.y < 0.f ? 2u : 0u) | (r.d.z < 0.f ? 4u : 0u));
+    const uint32_t octinv = 7u ^ ((dir[0].x < 0.f ? 1u : 0u) | (dir[0].y < 0.f ? 2u : 0u) | (dir[0].z < 0.f ? 4u : 0u));
     const uint32_t oct = __shfl_sync(kFull, octinv, 0);
     const uint32_t a_lut = opaque(sm_lut + oct * 256u);
 
-    TraceHit hit;
-    hit.t = __int_as_float(0x7f800000);
-    hit.tri = 0xFFFFFFFFu;
-    hit.prim = 0xFFFFFFFFu;
+    TraceHit hit[kRays];
+#pragma unroll
+    for (int j = 0; j < kRays; ++j) {
+      hit[j].t = __int_as_float(0x7f800000);
+      hit[j].tri = 0xFFFFFFFFu;
+      hit[j].prim = 0xFFFFFFFFu;
+    }
     float kmax = __int_as_float(0x7f800000);
     uint2 ngroup = make_uint2(0u, 0x80000000u), sreg = make_uint2(0u, 0u);
     int sp = 0, cost = 0;
@@ -233,19 +244,26 @@ __global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_ker
           const uint32_t tri = tri_base + (uint32_t)__popc(tri_valid & (low - 1u));
           const uint4 ua = lds_u128(src), ub = lds_u128(src + 16u), uc = lds_u128(src + 32u);
           src += 48u;
-          float t;
-          if (tri_test(mk3(__uint_as_float(ua.x), __uint_as_float(ua.y), __uint_as_float(ua.z)),
-                       mk3(__uint_as_float(ub.x), __uint_as_float(ub.y), __uint_as_float(ub.z)),
-                       mk3(__uint_as_float(uc.x), __uint_as_float(uc.y), __uint_as_float(uc.z)), r.o, r.d, t) &&
-              t >= p.ip.tnear && (t < hit.t || (t == hit.t && ua.w < hit.prim))) {  // tri_step<false>'s closest-hit rule
-            hit.t = t;
-            hit.tri = tri;
-            hit.prim = ua.w;
+          const f3 tv0 = mk3(__uint_as_float(ua.x), __uint_as_float(ua.y), __uint_as_float(ua.z));
+          const f3 te1 = mk3(__uint_as_float(ub.x), __uint_as_float(ub.y), __uint_as_float(ub.z));
+          const f3 te2 = mk3(__uint_as_float(uc.x), __uint_as_float(uc.y), __uint_as_float(uc.z));
+#pragma unroll
+          for (int j = 0; j < kRays; ++j) {
+            float t;
+            if (tri_test(tv0, te1, te2, O, dir[j], t) && t >= p.ip.tnear &&
+                (t < hit[j].t || (t == hit[j].t && ua.w < hit[j].prim))) {  // tri_step<false>'s closest-hit rule
+              hit[j].t = t;
+              hit[j].tri = tri;
+              hit[j].prim = ua.w;
+            }
           }
           cost += 4;
           if (kCount) ++n_tris;
         } while (tmask);
-        kmax = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(hit.t * w))) * 1.00001f;
+        float far = hit[0].t * w[0];
+#pragma unroll
+        for (int j = 1; j < kRays; ++j) far = fmaxf(far, hit[j].t * w[j]);
+        kmax = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(far))) * 1.00001f;
       }
       if (ngroup.y <= 0x00FFFFFFu) {
         if (sp == 0) break;
@@ -253,16 +271,20 @@ __global__ void __launch_bounds__(kPacketBlock, kBlocksPerSM) primary_packet_ker
         ngroup.x = __shfl_sync(kFull, sreg.x, sp);
         ngroup.y = __shfl_sync(kFull, sreg.y, sp);
       }
-      if (cost > a.budget) bail = true;
+      if (cost > a.budget * kRays) bail = true;
     }
     if (!bail) {
-      p.st.hit[id] = make_uint2(__float_as_uint(hit.tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit.t), hit.tri);
-      done_rays += 1u;
+#pragma unroll
+      for (int j = 0; j < kRays; ++j)
+        p.st.hit[id0 + (uint32_t)j * id_step] =
+            make_uint2(__float_as_uint(hit[j].tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit[j].t), hit[j].tri);
+      done_rays += (uint32_t)kRays;
     } else {
       uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(a.fb_count, 32u);
+      if (lane == 0) base = atomicAdd(a.fb_count, 32u * kRays);
       base = __shfl_sync(kFull, base, 0);
-      a.fb_queue[base + lane] = id;
+#pragma unroll
+      for (int j = 0; j < kRays; ++j) a.fb_queue[base + 32u * (uint32_t)j + lane] = id0 + (uint32_t)j * id_step;
       if (kCount) ++n_bail;
     }
   }
@@ -304,24 +326,26 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
   a.axis_k = k;
   a.sigma = f[k] < 0.0f ? -1.0f : 1.0f;
   a.budget = budget;
-  const uint32_t n_tasks = p.n_pixels * (p.samples / 32u);
+  const char* re = getenv("CUDAPT_PACKET_RAYS");  // rays per lane: 1, 2 or 4 (default: the largest that divides the pass)
+  const uint32_t chunks = p.samples / 32u;
+  int rays = re ? atoi(re) : 4;
+  rays = rays >= 4 && chunks % 4u == 0u ? 4 : (rays >= 2 && chunks % 2u == 0u ? 2 : 1);
+  const uint32_t n_tasks = p.n_pixels * (chunks / (uint32_t)rays);
   const uint32_t warps_per_cta = kPacketWarps;
-  const char* ke = getenv("CUDAPT_PACKET_BLOCKS");  // register budget: CTAs per SM the kernel is compiled for
-  const int bps = ke ? atoi(ke) : 8;
-  uint32_t grid = (uint32_t)sm_count * (uint32_t)(bps == 12 ? 12 : (bps == 10 ? 10 : 8));
+  uint32_t grid = (uint32_t)sm_count * (rays == 1 ? 8u : (rays == 2 ? 6u : 4u));
   const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;
   if (need < grid) grid = need ? need : 1u;
-#define PK_LAUNCH(B)                                                     \
+#define PK_LAUNCH(R)                                                     \
   if (counting)                                                          \
-    primary_packet_kernel<true, B><<<grid, kPacketBlock, 0, s>>>(a);     \
+    primary_packet_kernel<true, R><<<grid, kPacketBlock, 0, s>>>(a);     \
   else                                                                   \
-    primary_packet_kernel<false, B><<<grid, kPacketBlock, 0, s>>>(a)
-  if (bps == 12) {
-    PK_LAUNCH(12);
-  } else if (bps == 10) {
-    PK_LAUNCH(10);
+    primary_packet_kernel<false, R><<<grid, kPacketBlock, 0, s>>>(a)
+  if (rays == 4) {
+    PK_LAUNCH(4);
+  } else if (rays == 2) {
+    PK_LAUNCH(2);
   } else {
-    PK_LAUNCH(8);
+    PK_LAUNCH(1);
   }
 #undef PK_LAUNCH
   return cudaGetLastError();

@@ -72,6 +72,20 @@ def test_packets_equal_per_ray_kernel_and_twin(pt, oracle, scenes, name, monkeyp
     assert ok.mean() >= 0.9999 and same >= 0.995
 
 
+@pytest.mark.parametrize("rays", [1, 2, 4])
+def test_packets_of_32_64_128_samples(pt, scenes, rays, monkeypatch):
+    """128-sample passes: 1, 2 or 4 rays per lane (CUDAPT_PACKET_RAYS) -- the same image as the per-ray kernel."""
+    scene = scenes.heightfield(n_quads=48)
+    kw = dict(max_bounces=3, jitter=1, seed=13)
+    monkeypatch.setenv("CUDAPT_PRIMARY_PACKETS", "0")
+    a0, p0, t0, s0 = render(pt, scene, 64, 36, 128, 128, **kw)
+    monkeypatch.setenv("CUDAPT_PRIMARY_PACKETS", "1")
+    monkeypatch.setenv("CUDAPT_PACKET_RAYS", str(rays))
+    a1, p1, t1, s1 = render(pt, scene, 64, 36, 128, 128, **kw)
+    assert s1.packet_rays > 0.9 * 64 * 36 * 128 and s1.rays == s0.rays
+    assert np.array_equal(p1, p0) and np.array_equal(bits(t1), bits(t0)) and np.array_equal(bits(a1), bits(a0))
+
+
 def test_packets_rotated_camera_and_partition(pt, scenes, monkeypatch):
     """Camera looking down -Y/-X-ish (dominant axis and sign differ from the default +Z), 3-rank tile partition."""
     scene = scenes.heightfield(n_quads=64)
