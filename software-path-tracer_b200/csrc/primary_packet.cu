@@ -144,11 +144,10 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
         jx = jit.u0, jy = jit.u1;
       }
       dir[j] = primary_dir(p.cam, p.im, x, y, jx, jy);
-      p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);
+      // the origin {camera, tnear} of a camera ray is implied and queue 0 is the identity when every pixel is owned
+      // (shade_kernel, wavefront.cu): neither is stored
       p.st.ray_d[id] = make_float4(dir[j].x, dir[j].y, dir[j].z, __int_as_float(0x7f800000));
-      if (p.im.part_world <= 1u) {
-        p.st.queue[0][id] = id;
-      } else {
+      if (p.im.part_world > 1u) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
         base = __shfl_sync(kFull, base, 0);
@@ -284,7 +283,11 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       if (lane == 0) base = atomicAdd(a.fb_count, 32u * kRays);
       base = __shfl_sync(kFull, base, 0);
 #pragma unroll
-      for (int j = 0; j < kRays; ++j) a.fb_queue[base + 32u * (uint32_t)j + lane] = id0 + (uint32_t)j * id_step;
+      for (int j = 0; j < kRays; ++j) {
+        const uint32_t id = id0 + (uint32_t)j * id_step;
+        a.fb_queue[base + 32u * (uint32_t)j + lane] = id;
+        p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);  // the per-ray kernel reads its rays from memory
+      }
       if (kCount) ++n_bail;
     }
   }

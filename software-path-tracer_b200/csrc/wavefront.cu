@@ -146,22 +146,27 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
   // fetched two rounds ahead and the hit record one round ahead, so a round starts with both in registers and its
   // critical path is (ray state | triangle) -> material instead of four dependent loads (profiles/r01_notes.md:
   // the kernel was latency bound, long_scoreboard 7.2 per issue at 50 % issue utilisation).
-  uint32_t path_1 = i < n ? qin[i] : 0u;                    // entry of this round
-  uint32_t path_2 = i + stride < n ? qin[i + stride] : 0u;  // entry of the next round
+  // Camera rays traced as packets (p.chunked): queue 0 is the identity when every pixel is owned and is not stored,
+  // and the ray origin {camera, tnear} is implied (primary_packet.cu stores it only for its fall-back rays).
+  const bool camera_implied = a.bounce == 0 && p.chunked != 0u;
+  const bool ident = camera_implied && p.im.part_world <= 1u;
+  uint32_t path_1 = i < n ? (ident ? i : qin[i]) : 0u;                             // entry of this round
+  uint32_t path_2 = i + stride < n ? (ident ? i + stride : qin[i + stride]) : 0u;  // entry of the next round
   uint2 hit_1 = st.hit[path_1];
   for (uint32_t k = 0; k < rounds; ++k, i += stride) {
     bool cont = false, shadow = false;
     const uint32_t path = path_1;
     const uint2 h = hit_1;
     path_1 = path_2;
-    path_2 = (k + 2 < rounds && i + 2 * stride < n) ? qin[i + 2 * stride] : 0u;
+    path_2 = (k + 2 < rounds && i + 2 * stride < n) ? (ident ? i + 2 * stride : qin[i + 2 * stride]) : 0u;
     if (k + 1 < rounds) hit_1 = st.hit[path_1];  // path_1 was loaded a round ago: no stall here
     if (i < n) {
       uint32_t s, pixel;
       path_decode(p, path, pixel, s);
       const uint32_t frame = p.first_frame + s * p.frame_stride;
       const float t = __uint_as_float(h.x);
-      const float4 o4 = st.ray_o[path], d4 = st.ray_d[path];
+      const float4 o4 = camera_implied ? make_float4(p.cam.origin.x, p.cam.origin.y, p.cam.origin.z, p.ip.tnear) : st.ray_o[path];
+      const float4 d4 = st.ray_d[path];
       const float4 thr4 = a.bounce == 0 ? make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(kFlagSpecular)) : st.thr[path];
       f3 o = mk3(o4.x, o4.y, o4.z);
       const f3 d = mk3(d4.x, d4.y, d4.z);

@@ -30,9 +30,9 @@ for b in budgets:
             tr.render(spp)
         st = tr.stats()
         if not counting:
-            print(f"{name} spp {spp} budget {b}: render {st.last_render_ms:.3f} ms, trace launches {st.last_trace_ms:.3f} ms", flush=True)
+            print(f"{name} spp {spp} budget {b}: render {st.last_render_ms:.3f} ms, trace launches {st.last_trace_ms:.3f} ms, packets {st.last_packet_ms:.3f} ms", flush=True)
         else:
             npk = wl["w"] * wl["h"] * (spp // 32)
-            print(f"   per packet: nodes {st.packet_nodes / 2 / npk:.2f} tris {st.packet_tris / 2 / npk:.2f} bails {st.packet_bails / 2 / npk:.4f}"
+            print(f"   per packet: nodes {st.packet_nodes / npk:.2f} tris {st.packet_tris / npk:.2f} bails {st.packet_bails / npk:.4f}"
                   f" | per-ray kernel: nodes/ray {st.nodes_visited / max(st.rays, 1):.2f} tris/ray {st.tris_tested / max(st.rays, 1):.2f}", flush=True)
     tr.close()
