@@ -25,7 +25,7 @@ def load(path):
 if __name__ == "__main__":
     seq = load(sys.argv[1])
     which = int(sys.argv[2]) if len(sys.argv) > 2 else -2
-    starts = [i for i, l in enumerate(seq) if l["name"].startswith("raygen")]
+    starts = [i for i, l in enumerate(seq) if l["name"].startswith("raygen") or l["name"].startswith("primary_packet")]
     s0 = starts[which]
     s1 = starts[which + 1] if which + 1 < len(starts) and which != -1 else len(seq)
     tot = collections.Counter()
