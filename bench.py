@@ -42,7 +42,7 @@ WORKLOADS = {
                fov=1.0, kind="mesh"),
     "c5": dict(desc="configs[4]: the 1,002,528-triangle scene at 3840x2160, 1024 spp IN TOTAL sharded over the ranks "
                     "(sample ranges), accumulation combined at the read-back boundary",
-               w=3840, h=2160, spp=1024, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=32),
+               w=3840, h=2160, spp=1024, cfg=dict(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=64),
                fov=1.0, kind="mesh", strong=True),
 }
 DEFAULT_WORKLOAD = "c3"
@@ -303,10 +303,11 @@ def main():
         cs = tr.stats()
         # nodes_visited / tris_tested are counted by the per-ray kernel only: closest-hit rays it traced + shadow rays
         per_ray = max(cs.rays - cs.packet_rays, 1)
-        n_pk = max(cs.packet_rays // 32 + cs.packet_bails, 1)
+        n_pk = max(cs.packets + cs.packet_bails, 1)
         tr._counted = {"nodes_per_ray": cs.nodes_visited / per_ray, "tris_per_ray": cs.tris_tested / per_ray,
                        "packet_nodes": cs.packet_nodes / n_pk, "packet_tris": cs.packet_tris / n_pk,
-                       "packet_bail_frac": cs.packet_bails / n_pk if cs.packet_rays or cs.packet_bails else None}
+                       "packet_bail_frac": cs.packet_bails / n_pk if cs.packet_rays or cs.packet_bails else None,
+                       "rays_per_packet": cs.packet_rays / max(cs.packets, 1)}
         tr.set_counting(False)
     for _ in range(args.warmup):
         step()
@@ -364,9 +365,13 @@ def main():
     e2e_step()
     sync_all()
     t0 = time.perf_counter()
+    e2e_marks = []
     for _ in range(args.steps):
         e2e_step()
+        e2e_marks.append(time.perf_counter())
     sync_all()
+    if os.environ.get("BENCH_DEBUG"):
+        print(f"[rank {rank}] e2e step s {[round(b - a, 4) for a, b in zip([t0] + e2e_marks[:-1], e2e_marks)]}", file=sys.stderr, flush=True)
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
@@ -462,8 +467,8 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
     rays = float(st.rays)
     closest_rays = float(st.rays - st.shadow_rays - st.packet_rays)
     per_ray_rays = float(st.rays - st.packet_rays)
-    n_packets = st.packet_rays / 32.0
-    pk_bytes = n_packets * (counted["packet_nodes"] * 80.0 + counted["packet_tris"] * 48.0 + 32 * 44.0)
+    n_packets = float(st.packets)
+    pk_bytes = n_packets * (counted["packet_nodes"] * 80.0 + counted["packet_tris"] * 48.0) + st.packet_rays * 24.0
     bytes_per_path = (per_ray_rays * (Nn * 80.0 + Nt * 48.0) + pk_bytes) / paths + B * 160.0 + 32.0
     trace_ms = float(st.last_trace_ms)
     n_launches = max(1, -(-spp // int(wl["cfg"].get("samples_per_pass", 1))) * int(wl["cfg"].get("max_bounces", 4)))
@@ -479,7 +484,7 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
     if st.packet_rays:
         packets = {"kernel": "primary_packet_kernel", "share_of_step": st.last_packet_ms / render_ms if render_ms else None,
                    "ms_per_step": st.last_packet_ms, "camera_rays_finished": int(st.packet_rays),
-                   "node_steps_per_packet": counted["packet_nodes"], "triangle_steps_per_packet": counted["packet_tris"],
+                   "rays_per_packet": counted["rays_per_packet"], "node_steps_per_packet": counted["packet_nodes"], "triangle_steps_per_packet": counted["packet_tris"],
                    "handed_to_per_ray_kernel": counted["packet_bail_frac"],
                    "algorithmic_GBps": pk_bytes / (st.last_packet_ms * 1e-3) / 1e9 if st.last_packet_ms else None,
                    "note": "one warp = 32 samples of a pixel: fused ray generation + shared BVH walk; issue bound "

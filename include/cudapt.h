@@ -105,6 +105,7 @@ typedef struct cudapt_stats {
   uint64_t packet_rays;      /* camera rays finished by packets (part of .rays; always counted)                    */
   uint64_t shadow_rays;      /* any-hit queries (part of .rays; always counted)                                    */
   double last_packet_ms;     /* CUDA-event time of the packet launches inside the most recent cudapt_render()      */
+  uint64_t packets;          /* packets finished (32, 64 or 128 camera rays each; always counted)                  */
 } cudapt_stats;
 
 /* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */

@@ -53,6 +53,7 @@ class Stats(ctypes.Structure):
         ("last_trace_ms", ctypes.c_double),
         ("packet_nodes", ctypes.c_uint64), ("packet_tris", ctypes.c_uint64), ("packet_bails", ctypes.c_uint64),
         ("packet_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64), ("last_packet_ms", ctypes.c_double),
+        ("packets", ctypes.c_uint64),
     ]
 
 

@@ -629,6 +629,7 @@ int cudapt_get_stats(cudapt_ctx* ctx, cudapt_stats* out) {
   out->packet_rays = c[kCntPacketRays];
   out->shadow_rays = c[kCntShadowRays];
   out->last_packet_ms = ctx->last_packet_ms;
+  out->packets = c[kCntPackets];
   out->shade_invocations = c[kCntShades];
   out->kernel_launches = ctx->launches;
   out->render_ms = ctx->render_ms;

@@ -15,6 +15,7 @@ enum CounterSlot : int {
   kCntPacketBail = 7,
   kCntPacketRays = 8,   // camera rays finished by packets (always counted; also included in kCntRays)
   kCntShadowRays = 9,   // any-hit queries (always counted; also included in kCntRays)
+  kCntPackets = 10,     // packets finished (32 * R rays each; always counted)
   kCntSlots = 12
 };
 

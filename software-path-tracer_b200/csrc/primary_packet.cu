@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   if (lane == 0 && wr) {
     atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
     atomicAdd(&p.counters[kCntPacketRays], (unsigned long long)wr);
+    atomicAdd(&p.counters[kCntPackets], (unsigned long long)(wr / (32u * kRays)));
   }
   if (kCount && lane == 0) {
     atomicAdd(&p.counters[kCntPacketNodes], (unsigned long long)n_nodes);

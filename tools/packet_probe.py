@@ -32,7 +32,7 @@ for b in budgets:
         if not counting:
             print(f"{name} spp {spp} budget {b}: render {st.last_render_ms:.3f} ms, trace launches {st.last_trace_ms:.3f} ms, packets {st.last_packet_ms:.3f} ms", flush=True)
         else:
-            npk = wl["w"] * wl["h"] * (spp // 32)
+            npk = max(st.packets + st.packet_bails, 1)
             print(f"   per packet: nodes {st.packet_nodes / npk:.2f} tris {st.packet_tris / npk:.2f} bails {st.packet_bails / npk:.4f}"
                   f" | per-ray kernel: nodes/ray {st.nodes_visited / max(st.rays, 1):.2f} tris/ray {st.tris_tested / max(st.rays, 1):.2f}", flush=True)
     tr.close()
