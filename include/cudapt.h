@@ -111,6 +111,11 @@ typedef struct cudapt_stats {
 /* ---- lifetime: CPUPathTracer ctor/dtor, CPT.cpp:25-41 ---------------------------------------------- */
 void cudapt_default_config(cudapt_config* cfg);
 void cudapt_default_camera(cudapt_camera* cam);
+/* Fills *cam from the parameters of the reference's placeholder render::Camera (Camera.h:14-20,33-36: setPosition,
+ * setTarget, setUp, setPerspective's vertical field of view in degrees).  position 0, target +Z, up +Y, 90 degrees
+ * gives cudapt_default_camera() exactly.  CUDAPT_ERR_INVALID for a zero view vector or an up vector parallel to it. */
+int cudapt_camera_look_at(cudapt_camera* cam, const float position[3], const float target[3], const float up[3],
+                          float vfov_degrees);
 int cudapt_create(const cudapt_config* cfg, cudapt_ctx** out);
 void cudapt_destroy(cudapt_ctx* ctx);
 /* Error text of the last failing call on ctx (ctx may be NULL for a failed cudapt_create). */

@@ -69,7 +69,7 @@ MATERIAL_DTYPE = np.dtype([("albedo", np.float32, 3), ("type", np.uint32), ("emi
 
 # every symbol include/cudapt.h declares (tests/test_abi.py checks the header and the .so against this)
 EXPORTS = [
-    "cudapt_default_config", "cudapt_default_camera", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
+    "cudapt_default_config", "cudapt_default_camera", "cudapt_camera_look_at", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
     "cudapt_reupload_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
@@ -99,6 +99,9 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_default_config.restype = None
     lib.cudapt_default_camera.argtypes = [ctypes.POINTER(Camera)]
     lib.cudapt_default_camera.restype = None
+    f3p = ctypes.POINTER(ctypes.c_float)
+    lib.cudapt_camera_look_at.argtypes = [ctypes.POINTER(Camera), f3p, f3p, f3p, ctypes.c_float]
+    lib.cudapt_camera_look_at.restype = i32
     lib.cudapt_create.argtypes = [ctypes.POINTER(Config), ctypes.POINTER(vp)]
     lib.cudapt_destroy.argtypes = [vp]
     lib.cudapt_destroy.restype = None
@@ -166,6 +169,16 @@ def default_camera(**kw) -> Camera:
             c.tan_half_fov = float(v)
         else:
             setattr(c, k, (ctypes.c_float * 3)(*[float(x) for x in v]))
+    return c
+
+
+def look_at(position, target, up=(0.0, 1.0, 0.0), vfov_degrees=90.0) -> Camera:
+    """The reference's placeholder Camera (setPosition / setTarget / setUp / setPerspective) as a cudapt_camera."""
+    c = Camera()
+    v3 = lambda x: (ctypes.c_float * 3)(*[float(t) for t in x])
+    rc = load_library().cudapt_camera_look_at(ctypes.byref(c), v3(position), v3(target), v3(up), float(vfov_degrees))
+    if rc != 0:
+        raise ValueError("look_at: degenerate camera (zero view vector, up parallel to it, or fov outside (0, 180))")
     return c
 
 

@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <new>
 #include <string>
@@ -188,6 +189,38 @@ void cudapt_default_camera(cudapt_camera* cam) {  // CPT.cpp:62-73
   cam->up[1] = 1.0f;
   cam->forward[2] = 1.0f;
   cam->tan_half_fov = 1.0f;
+}
+
+// The placeholder render::Camera of the reference (Camera.h:10-38, `#if 0`): setPosition / setTarget / setUp /
+// setPerspective(fov).  Basis in double, rounded once: forward = normalize(target - position), right =
+// normalize(up x forward), up' = forward x right; with position 0, target +Z, up +Y and 90 degrees this is the
+// hard-coded camera of CPT.cpp:62-73 exactly.
+int cudapt_camera_look_at(cudapt_camera* cam, const float position[3], const float target[3], const float up[3],
+                          float vfov_degrees) {
+  if (!cam || !position || !target || !up) return CUDAPT_ERR_INVALID;
+  if (!(vfov_degrees > 0.0f && vfov_degrees < 180.0f)) return CUDAPT_ERR_INVALID;
+  double f[3], r[3], u[3];
+  for (int k = 0; k < 3; ++k) f[k] = (double)target[k] - (double)position[k];
+  const double fl = std::sqrt(f[0] * f[0] + f[1] * f[1] + f[2] * f[2]);
+  if (!(fl > 0.0)) return CUDAPT_ERR_INVALID;
+  for (int k = 0; k < 3; ++k) f[k] /= fl;
+  r[0] = (double)up[1] * f[2] - (double)up[2] * f[1];
+  r[1] = (double)up[2] * f[0] - (double)up[0] * f[2];
+  r[2] = (double)up[0] * f[1] - (double)up[1] * f[0];
+  const double rl = std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+  if (!(rl > 1e-12)) return CUDAPT_ERR_INVALID;  // up parallel to the view direction
+  for (int k = 0; k < 3; ++k) r[k] /= rl;
+  u[0] = f[1] * r[2] - f[2] * r[1];
+  u[1] = f[2] * r[0] - f[0] * r[2];
+  u[2] = f[0] * r[1] - f[1] * r[0];
+  for (int k = 0; k < 3; ++k) {
+    cam->origin[k] = position[k];
+    cam->right[k] = (float)r[k];
+    cam->up[k] = (float)u[k];
+    cam->forward[k] = (float)f[k];
+  }
+  cam->tan_half_fov = vfov_degrees == 90.0f ? 1.0f : (float)std::tan((double)vfov_degrees * 0.5 * 3.14159265358979323846 / 180.0);
+  return CUDAPT_OK;
 }
 
 const char* cudapt_last_error(const cudapt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }

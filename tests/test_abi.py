@@ -88,3 +88,24 @@ def test_product_never_touches_the_oracle():
     mk = open(os.path.join(root, "Makefile")).read()
     link = [l for l in mk.splitlines() if "-shared" in l]
     assert link and all("oracle" not in l for l in link)
+
+
+def test_look_at_reproduces_the_default_camera_and_rejects_degenerate_input(pt):
+    """cudapt_camera_look_at mirrors the reference's placeholder Camera (Camera.h:14-20,33-36); its defaults are the
+    hard-coded camera of CPT.cpp:62-73.  Pure host arithmetic: no GPU needed."""
+    import numpy as np
+    d = pt.default_camera()
+    c = pt.look_at((0, 0, 0), (0, 0, 1), (0, 1, 0), 90.0)
+    for f in ("origin", "right", "up", "forward"):
+        assert list(getattr(c, f)) == list(getattr(d, f))
+    assert c.tan_half_fov == d.tan_half_fov == 1.0
+    c = pt.look_at((1, 2, 3), (4, -2, 9), (0, 1, 0), 60.0)
+    r, u, f = (np.array(list(getattr(c, k)), np.float64) for k in ("right", "up", "forward"))
+    assert abs(np.linalg.norm(r) - 1) < 1e-6 and abs(np.linalg.norm(u) - 1) < 1e-6 and abs(np.linalg.norm(f) - 1) < 1e-6
+    assert abs(r @ u) < 1e-6 and abs(r @ f) < 1e-6 and abs(u @ f) < 1e-6
+    assert np.allclose(np.cross(u, f), r, atol=1e-6)  # right-handed like the default (right = up x forward)
+    assert abs(c.tan_half_fov - np.tan(np.radians(30.0))) < 1e-6
+    import pytest
+    for bad in (((0, 0, 0), (0, 0, 0), (0, 1, 0), 90.0), ((0, 0, 0), (0, 2, 0), (0, 1, 0), 90.0), ((0, 0, 0), (0, 0, 1), (0, 1, 0), 180.0)):
+        with pytest.raises(ValueError):
+            pt.look_at(*bad)

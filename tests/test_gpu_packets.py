@@ -15,7 +15,7 @@ def bits(a):
 def render(pt, scene, W, H, N, S, cam=None, part=None, **kw):
     with pt.PathTracer(pt.default_config(rng_mode=1, samples_per_pass=S, **kw)) as tr:
         if cam:
-            tr.set_camera(pt.default_camera(**cam))
+            tr.set_camera(cam if isinstance(cam, pt.Camera) else pt.default_camera(**cam))
         tr.set_resolution(W, H)
         tr.upload_mesh(*scene)
         if part:
@@ -90,8 +90,9 @@ def test_packets_rotated_camera_and_partition(pt, scenes, monkeypatch):
     """Camera looking down -Y/-X-ish (dominant axis and sign differ from the default +Z), 3-rank tile partition."""
     scene = scenes.heightfield(n_quads=64)
     kw = dict(max_bounces=3, jitter=1, seed=11)
-    for cam in (look((0.0, 6.0, 10.0), (0.0, -1.0, 0.05), up_hint=(0.0, 0.0, 1.0)),
-                look((12.0, 1.0, 10.0), (-1.0, -0.3, 0.1))):
+    cams = (look((0.0, 6.0, 10.0), (0.0, -1.0, 0.05), up_hint=(0.0, 0.0, 1.0)), look((12.0, 1.0, 10.0), (-1.0, -0.3, 0.1)),
+            pt.look_at((-10.0, 3.0, 10.0), (0.0, -2.0, 10.0), (0.0, 1.0, 0.0), 50.0))  # +X dominant, narrow lens
+    for cam in cams:
         out = {}
         for on in ("1", "0"):
             monkeypatch.setenv("CUDAPT_PRIMARY_PACKETS", on)
@@ -105,3 +106,38 @@ def test_packets_rotated_camera_and_partition(pt, scenes, monkeypatch):
         a = render(pt, scene, 80, 48, 32, 32, part=(r, 3, 16, 8), **kw)[0]
         total = a if total is None else total + a
     assert np.array_equal(bits(total), bits(full))
+
+
+def test_packets_full_size_config3_bit_identical(pt, scenes, monkeypatch):
+    """BASELINE.json configs[2] at its full size (1,002,528 triangles, 1920x1080), one 64-sample pass: the packet path
+    (2 rays per lane + fall-back queue) and the per-ray kernel produce the same accumulation buffer bit for bit, the
+    same primary-hit AOV and the same ray count; an environment map and a refit do not disturb that."""
+    scene = scenes.heightfield()
+    v = scene[0]
+    assert len(scene[1]) == 1_002_528
+    W, H, N = 1920, 1080, 64
+    env = scenes.octahedral_environment(64, sun_dir=(0.3, 0.8, 0.5), sun_power=20.0, seed=4)
+    out = {}
+    for on in ("1", "0"):
+        monkeypatch.setenv("CUDAPT_PRIMARY_PACKETS", on)
+        with pt.PathTracer(pt.default_config(rng_mode=1, max_bounces=8, jitter=1, seed=3, samples_per_pass=64)) as tr:
+            tr.set_resolution(W, H)
+            tr.upload_mesh(*scene)
+            tr.render(N)
+            a = tr.read_accum()[0]
+            prim, t = tr.read_primary_hits()
+            st = tr.stats()
+            tr.upload_environment(env)
+            w2 = v.copy()
+            w2[:, 1] += (0.05 * np.sin(2.0 * v[:, 0])).astype(np.float32)
+            tr.update_vertices(w2)
+            tr.render(N)
+            b = tr.read_accum()[0]
+        out[on] = (a, prim, t, st, b)
+    a1, p1, t1, s1, b1 = out["1"]
+    a0, p0, t0, s0, b0 = out["0"]
+    assert s1.packet_rays > 0.99 * W * H * N and s0.packet_rays == 0
+    assert s1.rays == s0.rays and s1.paths == s0.paths == W * H * N
+    assert np.array_equal(p1, p0) and np.array_equal(bits(t1), bits(t0))
+    assert np.array_equal(bits(a1), bits(a0))
+    assert np.array_equal(bits(b1), bits(b0)) and not np.array_equal(bits(b1), bits(a1))
