@@ -64,6 +64,8 @@ typedef struct cudapt_camera {
   float up[3];
   float forward[3];
   float tan_half_fov;
+  float lens_radius;     /* thin lens (Philox mode only): radius of the aperture disk in the right/up plane; 0 = pinhole */
+  float focus_distance;  /* distance along `forward` of the plane that is in focus (default 1; ignored for a pinhole)  */
 } cudapt_camera;
 
 typedef struct cudapt_config {

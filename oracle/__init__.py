@@ -122,6 +122,7 @@ class TwinParams(ctypes.Structure):
         ("cam_forward", ctypes.c_float * 3), ("cam_tan_half_fov", ctypes.c_float), ("threads", ctypes.c_int32),
         ("part_rank", ctypes.c_int32), ("part_world", ctypes.c_int32), ("tile_w", ctypes.c_int32),
         ("tile_h", ctypes.c_int32), ("env_rgb", ctypes.c_void_p), ("env_size", ctypes.c_int32),
+        ("cam_lens_radius", ctypes.c_float), ("cam_focus_distance", ctypes.c_float),
     ]
 
 

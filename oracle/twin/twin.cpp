@@ -119,11 +119,12 @@ inline void sincos2pi(float u, float& c, float& s) {
 struct Camera {
   V3 origin, right, up, forward;
   float tan_half_fov;
+  float lens_radius, focus_distance;
 };
 inline Camera camera_of(const twin_params& p) {
   return Camera{v3(p.cam_origin[0], p.cam_origin[1], p.cam_origin[2]), v3(p.cam_right[0], p.cam_right[1], p.cam_right[2]),
                 v3(p.cam_up[0], p.cam_up[1], p.cam_up[2]), v3(p.cam_forward[0], p.cam_forward[1], p.cam_forward[2]),
-                p.cam_tan_half_fov};
+                p.cam_tan_half_fov, p.rng_mode == 1 ? p.cam_lens_radius : 0.0f, p.cam_focus_distance};
 }
 // CPT.cpp:53-54,62-73 generalised: (jx,jy) is the sub-pixel offset (0 = reference corner sampling); with the
 // default basis/tan_half_fov the extra multiplies are by exactly 1 or 0 and the reference bits are kept.
@@ -139,6 +140,47 @@ inline V3 primary_dir(const Camera& cam, uint32_t x, uint32_t y, uint32_t W, uin
   const float cx = uv_x / len, cy = uv_y / len, cz = 1.0f / len;
   return v3((cx * cam.right.x + cy * cam.up.x) + cz * cam.forward.x, (cx * cam.right.y + cy * cam.up.y) + cz * cam.forward.y,
             (cx * cam.right.z + cy * cam.up.z) + cz * cam.forward.z);
+}
+// Thin lens (DESIGN.md "camera"): a point on the lens disk by REJECTION from the Philox stream -- candidates (2u-1, 2v-1)
+// from block 2 words 2,3, then blocks 3 and 4 (two candidates each), the first inside the unit disk wins, the lens
+// centre if none does (p = 4.6e-4) -- so that only + - * / sqrt and comparisons are needed and CPU and GPU agree bit
+// for bit.  The ray leaves origin + lx*right + ly*up towards the point where the pinhole ray of the same pixel sample
+// crosses the plane of focus.
+inline void primary_ray(const Camera& cam, uint32_t x, uint32_t y, uint32_t W, uint32_t H, float jx, float jy, const Rand4& j2,
+                        uint32_t pixel, uint32_t frame, uint32_t seed, V3* o, V3* d) {
+  if (!(cam.lens_radius > 0.0f)) {
+    *o = cam.origin;
+    *d = primary_dir(cam, x, y, W, H, jx, jy);
+    return;
+  }
+  float a = 0.0f, b = 0.0f;
+  bool found = false;
+  for (int c = 0; c < 5 && !found; ++c) {
+    float ua, ub;
+    if (c == 0) {
+      ua = j2.u[2], ub = j2.u[3];
+    } else {
+      const Rand4 q = philox_block(pixel, frame, 0, 3 + (uint32_t)(c - 1) / 2, seed);
+      ua = q.u[((c - 1) & 1) * 2], ub = q.u[((c - 1) & 1) * 2 + 1];
+    }
+    const float ca = ua * 2.0f - 1.0f, cb = ub * 2.0f - 1.0f;
+    if (ca * ca + cb * cb <= 1.0f) a = ca, b = cb, found = true;
+  }
+  const float lx = a * cam.lens_radius, ly = b * cam.lens_radius;
+  const float inv_height = 1.0f / H;
+  const float inv_width = 1.0f / W;
+  const float aspect_ratio = (float)W / (float)H;
+  const float u = ((float)x + jx) * inv_width;
+  const float v = 1.0f - ((float)y + jy) * inv_height;
+  const float uv_x = ((u * 2.0f - 1.0f) * aspect_ratio) * cam.tan_half_fov;
+  const float uv_y = (v * 2.0f - 1.0f) * cam.tan_half_fov;
+  const float fx = uv_x * cam.focus_distance - lx, fy = uv_y * cam.focus_distance - ly, fz = cam.focus_distance;
+  const float len = sqrtf((fx * fx + fy * fy) + fz * fz);
+  const float cx = fx / len, cy = fy / len, cz = fz / len;
+  *d = v3((cx * cam.right.x + cy * cam.up.x) + cz * cam.forward.x, (cx * cam.right.y + cy * cam.up.y) + cz * cam.forward.y,
+          (cx * cam.right.z + cy * cam.up.z) + cz * cam.forward.z);
+  *o = v3((cam.origin.x + lx * cam.right.x) + ly * cam.up.x, (cam.origin.y + lx * cam.right.y) + ly * cam.up.y,
+          (cam.origin.z + lx * cam.right.z) + ly * cam.up.z);
 }
 // CPT.cpp:286-292 with glm::mix(x, y, a) = x*(1-a) + y*a  (glm/detail/func_common.inl:140)
 inline V3 sample_sky(V3 d) {
@@ -709,6 +751,7 @@ void twin_default_params(twin_params* p) {
   p->cam_up[1] = 1.0f;
   p->cam_forward[2] = 1.0f;
   p->cam_tan_half_fov = 1.0f;
+  p->cam_focus_distance = 1.0f;
   p->part_world = 1;
   p->tile_w = 32;
   p->tile_h = 32;
@@ -730,15 +773,15 @@ int twin_render_spheres(const twin_params* pp, const float* sph, int32_t n, uint
         const uint32_t pixel = y * W + x;
         uint32_t rng = pcg_seed(x, y, W, frame);
         float jx = 0.0f, jy = 0.0f;
-        if (p.rng_mode == 1 && p.jitter) {
-          const Rand4 j = philox_block(pixel, frame, 0, 2, p.seed);
-          jx = j.u[0], jy = j.u[1];
-        }
-        const V3 d = primary_dir(cam, x, y, W, H, jx, jy);
+        Rand4 j{};
+        if (p.rng_mode == 1 && (p.jitter || cam.lens_radius > 0.0f)) j = philox_block(pixel, frame, 0, 2, p.seed);
+        if (p.rng_mode == 1 && p.jitter) jx = j.u[0], jy = j.u[1];
+        V3 o, d;
+        primary_ray(cam, x, y, W, H, jx, jy, j, pixel, frame, p.seed, &o, &d);
         int fi = -1;
         float ft = 0.0f;
         const bool cap = (k == 0) && primary_idx;
-        const V3 c = trace_spheres(p, sph, n, cam.origin, d, rng, pixel, frame, cnt, cap ? &fi : nullptr, &ft);
+        const V3 c = trace_spheres(p, sph, n, o, d, rng, pixel, frame, cnt, cap ? &fi : nullptr, &ft);
         ++cnt.paths;
         if (cap) {
           primary_idx[pixel] = fi;
@@ -809,15 +852,15 @@ int twin_render_mesh(const twin_params* pp, void* mesh, uint32_t first_frame, ui
         if (!owns_pixel(p, x, y)) continue;
         const uint32_t pixel = y * W + x;
         float jx = 0.0f, jy = 0.0f;
-        if (p.jitter) {
-          const Rand4 j = philox_block(pixel, frame, 0, 2, p.seed);
-          jx = j.u[0], jy = j.u[1];
-        }
-        const V3 d = primary_dir(cam, x, y, W, H, jx, jy);
+        Rand4 j{};
+        if (p.jitter || cam.lens_radius > 0.0f) j = philox_block(pixel, frame, 0, 2, p.seed);
+        if (p.jitter) jx = j.u[0], jy = j.u[1];
+        V3 o, d;
+        primary_ray(cam, x, y, W, H, jx, jy, j, pixel, frame, p.seed, &o, &d);
         int32_t fi = -1;
         float ft = 0.0f;
         const bool cap = (k == 0) && primary_idx;
-        const V3 c = trace_mesh(p, m, cam.origin, d, pixel, frame, cnt, cap ? &fi : nullptr, &ft);
+        const V3 c = trace_mesh(p, m, o, d, pixel, frame, cnt, cap ? &fi : nullptr, &ft);
         ++cnt.paths;
         if (cap) {
           primary_idx[pixel] = fi;

@@ -41,6 +41,8 @@ typedef struct twin_params {
    * the reference's procedural sky (CPT.cpp:286-292) */
   const float* env_rgb;
   int32_t env_size;
+  /* thin lens (mirrors cudapt_camera.lens_radius / focus_distance; Philox mode only): 0 = pinhole */
+  float cam_lens_radius, cam_focus_distance;
 } twin_params;
 
 typedef struct twin_material {

@@ -40,7 +40,8 @@ class Config(ctypes.Structure):
 
 class Camera(ctypes.Structure):
     _fields_ = [("origin", ctypes.c_float * 3), ("right", ctypes.c_float * 3), ("up", ctypes.c_float * 3),
-                ("forward", ctypes.c_float * 3), ("tan_half_fov", ctypes.c_float)]
+                ("forward", ctypes.c_float * 3), ("tan_half_fov", ctypes.c_float),
+                ("lens_radius", ctypes.c_float), ("focus_distance", ctypes.c_float)]
 
 
 class Stats(ctypes.Structure):
@@ -165,8 +166,8 @@ def default_camera(**kw) -> Camera:
     c = Camera()
     load_library().cudapt_default_camera(ctypes.byref(c))
     for k, v in kw.items():
-        if k == "tan_half_fov":
-            c.tan_half_fov = float(v)
+        if k in ("tan_half_fov", "lens_radius", "focus_distance"):
+            setattr(c, k, float(v))
         else:
             setattr(c, k, (ctypes.c_float * 3)(*[float(x) for x in v]))
     return c

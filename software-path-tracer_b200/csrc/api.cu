@@ -99,6 +99,8 @@ CameraParams camera_params(const cudapt_camera& c) {
   p.up = mk3(c.up[0], c.up[1], c.up[2]);
   p.forward = mk3(c.forward[0], c.forward[1], c.forward[2]);
   p.tan_half_fov = c.tan_half_fov;
+  p.lens_radius = c.lens_radius > 0.0f ? c.lens_radius : 0.0f;
+  p.focus_distance = c.focus_distance;
   return p;
 }
 
@@ -189,6 +191,7 @@ void cudapt_default_camera(cudapt_camera* cam) {  // CPT.cpp:62-73
   cam->up[1] = 1.0f;
   cam->forward[2] = 1.0f;
   cam->tan_half_fov = 1.0f;
+  cam->focus_distance = 1.0f;
 }
 
 // The placeholder render::Camera of the reference (Camera.h:10-38, `#if 0`): setPosition / setTarget / setUp /
@@ -219,6 +222,8 @@ int cudapt_camera_look_at(cudapt_camera* cam, const float position[3], const flo
     cam->up[k] = (float)u[k];
     cam->forward[k] = (float)f[k];
   }
+  cam->lens_radius = 0.0f;
+  cam->focus_distance = (float)fl;  // the target is in focus once the caller opens the lens
   cam->tan_half_fov = vfov_degrees == 90.0f ? 1.0f : (float)std::tan((double)vfov_degrees * 0.5 * 3.14159265358979323846 / 180.0);
   return CUDAPT_OK;
 }

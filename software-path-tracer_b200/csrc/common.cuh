@@ -98,6 +98,7 @@ __device__ __forceinline__ void sincos2pi(float u, float& c, float& s) {
 struct CameraParams {
   f3 origin, right, up, forward;
   float tan_half_fov;
+  float lens_radius, focus_distance;  // thin lens (Philox mode only); lens_radius 0 = pinhole
 };
 struct ImageParams {
   uint32_t width, height;
@@ -117,6 +118,49 @@ __device__ __forceinline__ f3 primary_dir(const CameraParams& cam, const ImagePa
   return mk3((cx * cam.right.x + cy * cam.up.x) + cz * cam.forward.x,
              (cx * cam.right.y + cy * cam.up.y) + cz * cam.forward.y,
              (cx * cam.right.z + cy * cam.up.z) + cz * cam.forward.z);
+}
+// Camera ray of (pixel, frame) in Philox mode: sub-pixel jitter from block 2 words 0,1 and -- thin lens, SURVEY.md
+// 8f-1 -- a lens point by REJECTION from the same stream (block 2 words 2,3, then blocks 3 and 4, two candidates each;
+// the lens centre if all five fall outside the unit disk), so that only + - * / sqrt and comparisons are involved and
+// the CPU twin (oracle/twin/twin.cpp primary_ray) reproduces origin and direction bit for bit.
+__device__ __forceinline__ void primary_ray_philox(const CameraParams& cam, const ImageParams& im, bool jitter, uint32_t seed,
+                                                   uint32_t pixel, uint32_t frame, uint32_t x, uint32_t y, f3* o, f3* d) {
+  float jx = 0.0f, jy = 0.0f;
+  const bool lens = cam.lens_radius > 0.0f;
+  rand4 j;
+  j.u0 = j.u1 = j.u2 = j.u3 = 0.0f;
+  if (jitter || lens) j = philox_block(pixel, frame, 0u, 2u, seed);
+  if (jitter) jx = j.u0, jy = j.u1;
+  if (!lens) {
+    *o = cam.origin;
+    *d = primary_dir(cam, im, x, y, jx, jy);
+    return;
+  }
+  float a = 0.0f, b = 0.0f;
+  bool found = false;
+  for (int c = 0; c < 5 && !found; ++c) {
+    float ua, ub;
+    if (c == 0) {
+      ua = j.u2, ub = j.u3;
+    } else {
+      const rand4 q = philox_block(pixel, frame, 0u, 3u + (uint32_t)(c - 1) / 2u, seed);
+      ua = ((c - 1) & 1) ? q.u2 : q.u0, ub = ((c - 1) & 1) ? q.u3 : q.u1;
+    }
+    const float ca = ua * 2.0f - 1.0f, cb = ub * 2.0f - 1.0f;
+    if (ca * ca + cb * cb <= 1.0f) a = ca, b = cb, found = true;
+  }
+  const float lx = a * cam.lens_radius, ly = b * cam.lens_radius;
+  const float u = ((float)x + jx) * im.inv_width;
+  const float v = 1.0f - ((float)y + jy) * im.inv_height;
+  const float uv_x = ((u * 2.0f - 1.0f) * im.aspect) * cam.tan_half_fov;
+  const float uv_y = (v * 2.0f - 1.0f) * cam.tan_half_fov;
+  const float fx = uv_x * cam.focus_distance - lx, fy = uv_y * cam.focus_distance - ly, fz = cam.focus_distance;
+  const float len = sqrtf((fx * fx + fy * fy) + fz * fz);
+  const float cx = fx / len, cy = fy / len, cz = fz / len;
+  *d = mk3((cx * cam.right.x + cy * cam.up.x) + cz * cam.forward.x, (cx * cam.right.y + cy * cam.up.y) + cz * cam.forward.y,
+           (cx * cam.right.z + cy * cam.up.z) + cz * cam.forward.z);
+  *o = mk3((cam.origin.x + lx * cam.right.x) + ly * cam.up.x, (cam.origin.y + lx * cam.right.y) + ly * cam.up.y,
+           (cam.origin.z + lx * cam.right.z) + ly * cam.up.z);
 }
 // CPT.cpp:286-292; glm::mix(x, y, a) = x*(1-a) + y*a
 __device__ __forceinline__ f3 sample_sky(f3 d) {

@@ -312,7 +312,8 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
 bool primary_packets_enabled(const PassParams& p) {
   const char* e = getenv("CUDAPT_PRIMARY_PACKETS");  // read per pass: tests toggle it
   const int on = e ? atoi(e) : 1;
-  return on != 0 && p.samples >= 32u && p.samples % 32u == 0u;
+  // a thin lens gives every ray its own origin: no common apex, no packets
+  return on != 0 && p.samples >= 32u && p.samples % 32u == 0u && !(p.cam.lens_radius > 0.0f);
 }
 
 cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,

@@ -96,10 +96,8 @@ __global__ void __launch_bounds__(kSphereBlockX* kSphereBlockY)
     uint32_t frame = a.first_frame;
     uint32_t rng = pcg_seed(x, y, a.im.width, frame);
     f3 o = a.cam.origin, d = d0;
-    if (kPhilox && a.ip.jitter) {
-      const rand4 j = philox_block(pixel, frame, 0u, 2u, a.ip.seed);
-      d = primary_dir(a.cam, a.im, x, y, j.u0, j.u1);
-    }
+    if (kPhilox && (a.ip.jitter || a.cam.lens_radius > 0.0f))
+      primary_ray_philox(a.cam, a.im, a.ip.jitter != 0, a.ip.seed, pixel, frame, x, y, &o, &d);
     f3 thr = mk3(1.f, 1.f, 1.f);
     f3 L = mk3(0.f, 0.f, 0.f);
     int bounce = 0;
@@ -161,10 +159,8 @@ __global__ void __launch_bounds__(kSphereBlockX* kSphereBlockY)
         rng = pcg_seed(x, y, a.im.width, frame);
         o = a.cam.origin;
         d = d0;
-        if (kPhilox && a.ip.jitter) {
-          const rand4 j = philox_block(pixel, frame, 0u, 2u, a.ip.seed);
-          d = primary_dir(a.cam, a.im, x, y, j.u0, j.u1);
-        }
+        if (kPhilox && (a.ip.jitter || a.cam.lens_radius > 0.0f))
+          primary_ray_philox(a.cam, a.im, a.ip.jitter != 0, a.ip.seed, pixel, frame, x, y, &o, &d);
         thr = mk3(1.f, 1.f, 1.f);
         L = mk3(0.f, 0.f, 0.f);
         bounce = 0;

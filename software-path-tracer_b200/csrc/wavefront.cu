@@ -100,13 +100,9 @@ __global__ void __launch_bounds__(kShadeBlock) raygen_kernel(const PassParams p)
     }
     if (live) {
       const uint32_t frame = p.first_frame + s * p.frame_stride;
-      float jx = 0.0f, jy = 0.0f;
-      if (p.ip.jitter) {
-        const rand4 j = philox_block(pixel, frame, 0u, 2u, p.ip.seed);
-        jx = j.u0, jy = j.u1;
-      }
-      const f3 d = primary_dir(p.cam, p.im, x, y, jx, jy);
-      p.st.ray_o[id] = make_float4(p.cam.origin.x, p.cam.origin.y, p.cam.origin.z, p.ip.tnear);
+      f3 o, d;
+      primary_ray_philox(p.cam, p.im, p.ip.jitter != 0, p.ip.seed, pixel, frame, x, y, &o, &d);
+      p.st.ray_o[id] = make_float4(o.x, o.y, o.z, p.ip.tnear);
       p.st.ray_d[id] = make_float4(d.x, d.y, d.z, __int_as_float(0x7f800000));
       // throughput (1,1,1 | specular) and radiance 0 of a camera ray are implied at bounce 0: not stored
     }

@@ -3,7 +3,8 @@
  * also the proof that the header is a C header.
  *
  *   cudapt_cli [--scene app | --obj FILE] [--size WxH] [--spp N] [--bounces N] [--philox] [--jitter]
- *              [--exposure X] [--auto-exposure] [--tonemap none|reinhard|aces] [--srgb] [--device D] --out FILE.ppm|.pfm
+ *              [--exposure X] [--auto-exposure] [--tonemap none|reinhard|aces] [--srgb] [--device D]
+ *              [--look-at px,py,pz,tx,ty,tz,vfov] [--lens RADIUS] --out FILE.ppm|.pfm
  *
  * --scene app : the 38 spheres of App.cpp:101-122 with the reference integrator (default).
  * --obj FILE  : triangles of a Wavefront OBJ ("v" and "f" records; polygons are fanned), one grey Lambert material,
@@ -79,10 +80,13 @@ int main(int argc, char** argv) {
   cudapt_ctx* ctx = NULL;
   cudapt_config cfg;
   cudapt_postprocess post;
+  cudapt_camera cam;
+  int have_cam = 0;
   const char *out = NULL, *obj = NULL;
   unsigned w = 640, h = 360, spp = 16;
   cudapt_default_config(&cfg);
   cudapt_default_postprocess(&post);
+  cudapt_default_camera(&cam);
   for (int i = 1; i < argc; ++i) {
     const char* a = argv[i];
     const char* nx = i + 1 < argc ? argv[i + 1] : "";
@@ -98,6 +102,16 @@ int main(int argc, char** argv) {
     else if (!strcmp(a, "--exposure")) post.exposure = (float)atof(nx), ++i;
     else if (!strcmp(a, "--auto-exposure")) post.auto_exposure = 1;
     else if (!strcmp(a, "--srgb")) post.srgb = 1;
+    else if (!strcmp(a, "--look-at")) { /* the reference's placeholder Camera: position, target, vertical fov */
+      float q[7];
+      const float up[3] = {0.f, 1.f, 0.f};
+      if (sscanf(nx, "%f,%f,%f,%f,%f,%f,%f", &q[0], &q[1], &q[2], &q[3], &q[4], &q[5], &q[6]) != 7 ||
+          cudapt_camera_look_at(&cam, q, q + 3, up, q[6]) != CUDAPT_OK) {
+        fprintf(stderr, "cudapt_cli: bad --look-at\n");
+        return 2;
+      }
+      have_cam = 1, ++i;
+    } else if (!strcmp(a, "--lens")) cam.lens_radius = (float)atof(nx), cfg.rng_mode = CUDAPT_RNG_PHILOX, have_cam = 1, ++i;
     else if (!strcmp(a, "--tonemap")) {
       post.tonemap = !strcmp(nx, "aces") ? CUDAPT_TONEMAP_ACES : !strcmp(nx, "reinhard") ? CUDAPT_TONEMAP_REINHARD : CUDAPT_TONEMAP_NONE;
       ++i;
@@ -116,6 +130,7 @@ int main(int argc, char** argv) {
   }
   if (cudapt_create(&cfg, &ctx) != CUDAPT_OK) die(NULL, "cudapt_create");
   CHECK(cudapt_set_resolution(ctx, w, h));
+  if (have_cam) CHECK(cudapt_set_camera(ctx, &cam));
   if (obj) {
     float* v;
     uint32_t *t, nv, nt;
