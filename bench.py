@@ -345,12 +345,17 @@ def main():
     # ---- e2e through the C ABI with host buffers: scene H2D + render + resolve + RGBA8 D2H every step ----
     host_rgba = np.empty((H, W), np.uint32)
 
-    def e2e_step():
+    def e2e_step(first=True, last=True):
+        # The step's scene goes host -> device inside the timed region.  Mesh scenes are double-buffered: the copy for
+        # step k+1 (cudapt_stage_scene, the library's copy stream) is started as soon as step k's kernels are queued and
+        # overlaps them; step k+1's render waits for it and swaps the buffers.  The first step uploads in line.
         if wl["kind"] == "spheres":
             tr.upload_spheres(scene["spheres"])     # H2D of the step's scene; also restarts accumulation
-        else:
+        elif first:
             tr.reupload_scene()
         tr.render(spp)
+        if wl["kind"] == "mesh" and not last:
+            tr.stage_scene()                         # next step's scene: H2D concurrent with this step's rendering
         tail()
         if world > 1:
             tr.set_frame_count(spp * world if rank == 0 else spp)
@@ -366,8 +371,8 @@ def main():
     sync_all()
     t0 = time.perf_counter()
     e2e_marks = []
-    for _ in range(args.steps):
-        e2e_step()
+    for k in range(args.steps):
+        e2e_step(first=(k == 0), last=(k == args.steps - 1))   # exactly one scene upload per step
         e2e_marks.append(time.perf_counter())
     sync_all()
     if os.environ.get("BENCH_DEBUG"):

@@ -149,6 +149,11 @@ int cudapt_build_accel(cudapt_ctx* ctx);
  * changed on the host without changing topology (the reference re-commits its Embree scene whenever
  * Scene::hasChanges(), CPT.cpp:122-131,156-160). */
 int cudapt_reupload_scene(cudapt_ctx* ctx);
+/* The same copy, DOUBLE-BUFFERED: starts copying the scene into a second device copy on the library's copy stream and
+ * returns at once; rendering that is in flight keeps reading the current copy.  The new copy becomes the scene at the
+ * next cudapt_render() (or scene call), which waits for the transfer and restarts accumulation.  This is how a host
+ * that rewrites the scene every frame overlaps the upload of frame k+1 with the rendering of frame k. */
+int cudapt_stage_scene(cudapt_ctx* ctx);
 /* Incremental scene update: the triangle mesh keeps its indices and materials, the nv vertices
  * (same count as uploaded) move.  The BVH is REFIT on the host -- tree, child slots and triangle order are kept,
  * every box and quantisation grid is recomputed bottom-up -- and uploaded again; accumulation restarts.  This is

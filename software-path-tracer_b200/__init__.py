@@ -73,7 +73,7 @@ EXPORTS = [
     "cudapt_default_config", "cudapt_default_camera", "cudapt_camera_look_at", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
-    "cudapt_reupload_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
+    "cudapt_reupload_scene", "cudapt_stage_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
     "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
@@ -117,6 +117,7 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_upload_materials.argtypes = [vp, vp, u32]
     lib.cudapt_build_accel.argtypes = [vp]
     lib.cudapt_reupload_scene.argtypes = [vp]
+    lib.cudapt_stage_scene.argtypes = [vp]
     lib.cudapt_update_vertices.argtypes = [vp, vp, u32]
     lib.cudapt_debug_accel_checksum.argtypes = [vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
     lib.cudapt_reset.argtypes = [vp]
@@ -275,6 +276,10 @@ class PathTracer:
 
     def reupload_scene(self):
         self._chk(self._lib.cudapt_reupload_scene(self._h))
+
+    def stage_scene(self):
+        """Double-buffered re-upload: returns at once, takes effect (and restarts accumulation) at the next render."""
+        self._chk(self._lib.cudapt_stage_scene(self._h))
 
     def upload_environment(self, rgb):
         """Octahedral environment map, (n, n, 3) float32; None restores the procedural sky."""

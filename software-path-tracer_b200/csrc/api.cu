@@ -387,19 +387,38 @@ int cudapt_build_accel(cudapt_ctx* ctx) {
   return restart_accumulation(ctx);
 }
 
+// a staged scene (cudapt_stage_scene) takes effect before anything else touches the scene
+static int commit_staged_scene(cudapt_ctx* ctx) {
+  if (ctx->scene != cudapt_ctx::kMesh || !ctx->mesh.swap_pending()) return CUDAPT_OK;
+  std::string err;
+  if (!ctx->mesh.commit_staged(ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_CUDA, "staged scene: %s", err.c_str());
+  return restart_accumulation(ctx);
+}
+
 int cudapt_reupload_scene(cudapt_ctx* ctx) {
   if (!ctx) return CUDAPT_ERR_INVALID;
   if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_reupload_scene: no built mesh scene");
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  if (int rc = commit_staged_scene(ctx)) return rc;
   std::string err;
   if (!ctx->mesh.reupload(ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_reupload_scene: %s", err.c_str());
   return restart_accumulation(ctx);
+}
+
+int cudapt_stage_scene(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_stage_scene: no built mesh scene");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  std::string err;
+  if (!ctx->mesh.stage(ctx->stream, &err)) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_stage_scene: %s", err.c_str());
+  return CUDAPT_OK;
 }
 
 int cudapt_update_vertices(cudapt_ctx* ctx, const float* vertices, uint32_t nv) {
   if (!ctx || !vertices) return CUDAPT_ERR_INVALID;
   if (ctx->scene != cudapt_ctx::kMesh) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_update_vertices: no built mesh scene");
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  if (int rc = commit_staged_scene(ctx)) return rc;
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // the pinned staging buffer may still be in flight
   std::string err;
   uint64_t launches = 0;
@@ -447,6 +466,7 @@ int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   int rc = finish_timing(ctx);
   if (rc) return rc;
+  if ((rc = commit_staged_scene(ctx)) != CUDAPT_OK) return rc;
   const uint32_t first = ctx->frame_first + ctx->frame_count * ctx->frame_stride;  // 1-based (CPT.cpp:61)
   const bool want_aov = ctx->frame_count == 0;
   CU_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));

@@ -23,6 +23,15 @@ struct MeshDevice {
   void* h_pinned = nullptr;  // nodes | tris, pinned, for cudapt_reupload_scene
   size_t pinned_bytes = 0;
   bool staging_stale = false;  // the device copy was refitted in place; refresh h_pinned before re-uploading from it
+  // double-buffered upload (cudapt_stage_scene): the NEXT version of nodes | tris is copied on its own stream while
+  // the current one is being rendered from; the buffers swap at the next render
+  uint4* d_nodes_shadow = nullptr;
+  float4* d_tris_shadow = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_copy_done = nullptr;
+  cudaEvent_t ev_last_use[2] = {nullptr, nullptr};  // last render that read buffer 0 / 1 (0 = the one built first)
+  int current = 0;
+  bool swap_pending = false;
   // device refit (refit.cu): caller-order vertices and indices, per-triangle and per-node boxes
   float* d_vertices = nullptr;
   uint32_t* d_indices = nullptr;
@@ -45,6 +54,15 @@ struct MeshDevice {
   void free_scene() {
     cudaFree(d_nodes), cudaFree(d_tris), cudaFree(d_materials), cudaFree(d_lights);
     d_nodes = nullptr, d_tris = nullptr, d_materials = nullptr, d_lights = nullptr;
+    cudaFree(d_nodes_shadow), cudaFree(d_tris_shadow);
+    d_nodes_shadow = nullptr, d_tris_shadow = nullptr;
+    if (copy_stream) cudaStreamDestroy(copy_stream);
+    if (ev_copy_done) cudaEventDestroy(ev_copy_done);
+    for (cudaEvent_t& e : ev_last_use) {
+      if (e) cudaEventDestroy(e);
+      e = nullptr;
+    }
+    copy_stream = nullptr, ev_copy_done = nullptr, current = 0, swap_pending = false;
     cudaFree(d_vertices), cudaFree(d_indices), cudaFree(d_tri_box), cudaFree(d_node_box);
     d_vertices = nullptr, d_indices = nullptr, d_tri_box = nullptr, d_node_box = nullptr;
     if (h_pinned_vertices) cudaFreeHost(h_pinned_vertices);
@@ -147,6 +165,51 @@ bool MeshScene::reupload(cudaStream_t stream, std::string* err) {
   const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
   MH_TRY(cudaMemcpyAsync(dev_->d_nodes, dev_->h_pinned, nb, cudaMemcpyHostToDevice, stream));
   MH_TRY(cudaMemcpyAsync(dev_->d_tris, (char*)dev_->h_pinned + nb, tb, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_materials, dev_->materials.data(), dev_->materials.size() * sizeof(cudapt_material),
+                         cudaMemcpyHostToDevice, stream));
+  if (!dev_->lights.empty())
+    MH_TRY(cudaMemcpyAsync(dev_->d_lights, dev_->lights.data(), dev_->lights.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                           stream));
+  return true;
+}
+
+// Double-buffered upload: start copying nodes | tris from the pinned staging into the SHADOW device copy on the copy
+// stream -- concurrently with whatever the render stream is doing -- and make it the scene at the next render.
+bool MeshScene::stage(cudaStream_t render_stream, std::string* err) {
+  if (!dev_ || !dev_->h_pinned) {
+    *err = "no built scene";
+    return false;
+  }
+  if (dev_->staging_stale && !refresh_staging(render_stream, err)) return false;
+  const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
+  if (!dev_->d_nodes_shadow) {
+    MH_TRY(cudaMalloc(&dev_->d_nodes_shadow, nb));
+    MH_TRY(cudaMalloc(&dev_->d_tris_shadow, tb));
+    MH_TRY(cudaStreamCreateWithFlags(&dev_->copy_stream, cudaStreamNonBlocking));
+    MH_TRY(cudaEventCreateWithFlags(&dev_->ev_copy_done, cudaEventDisableTiming));
+    for (cudaEvent_t& e : dev_->ev_last_use) MH_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    // the two events start signalled
+  }
+  // the shadow buffer may still be read by the last render that used it (never by the one in flight now)
+  MH_TRY(cudaStreamWaitEvent(dev_->copy_stream, dev_->ev_last_use[dev_->current ^ 1], 0));
+  MH_TRY(cudaMemcpyAsync(dev_->d_nodes_shadow, dev_->h_pinned, nb, cudaMemcpyHostToDevice, dev_->copy_stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_tris_shadow, (char*)dev_->h_pinned + nb, tb, cudaMemcpyHostToDevice, dev_->copy_stream));
+  MH_TRY(cudaEventRecord(dev_->ev_copy_done, dev_->copy_stream));
+  dev_->swap_pending = true;
+  return true;
+}
+
+bool MeshScene::swap_pending() const { return dev_ && dev_->swap_pending; }
+
+// Makes the staged copy the scene: the render stream waits for the copy, the buffers swap, the small arrays
+// (materials, light list) follow on the render stream.
+bool MeshScene::commit_staged(cudaStream_t stream, std::string* err) {
+  if (!dev_ || !dev_->swap_pending) return true;
+  MH_TRY(cudaStreamWaitEvent(stream, dev_->ev_copy_done, 0));
+  std::swap(dev_->d_nodes, dev_->d_nodes_shadow);
+  std::swap(dev_->d_tris, dev_->d_tris_shadow);
+  dev_->current ^= 1;
+  dev_->swap_pending = false;
   MH_TRY(cudaMemcpyAsync(dev_->d_materials, dev_->materials.data(), dev_->materials.size() * sizeof(cudapt_material),
                          cudaMemcpyHostToDevice, stream));
   if (!dev_->lights.empty())
@@ -396,6 +459,7 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     ++*launches;
     done += s;
   }
+  if (dev_->ev_last_use[dev_->current]) R_TRY(cudaEventRecord(dev_->ev_last_use[dev_->current], stream), "event record");
 #undef R_TRY
   return cudaSuccess;
 }

@@ -42,6 +42,10 @@ class MeshScene {
   double refit_ms = 0.0;
   // H2D copy of the packed scene (nodes, triangles, materials, lights) from pinned host memory.
   bool reupload(cudaStream_t stream, std::string* err);
+  // double-buffered upload (cudapt_stage_scene)
+  bool stage(cudaStream_t render_stream, std::string* err);
+  bool swap_pending() const;
+  bool commit_staged(cudaStream_t stream, std::string* err);
   cudaError_t render(const MeshRenderArgs& a, cudaStream_t stream, uint64_t* launches, std::string* err);
   void invalidate_image_state();
   void release();

@@ -119,3 +119,39 @@ def test_refit_time_at_one_million_triangles(pt, scenes, monkeypatch):
           f"(includes the numpy->pinned copy and the 6 MB vertex upload)")
     assert dev_ms < host_ms
     tr.close()
+
+
+def test_stage_scene_double_buffered_upload(pt, scenes, monkeypatch):
+    """cudapt_stage_scene copies the scene into the shadow buffers on the copy stream while a render is in flight; the
+    render in flight is not disturbed, the next render runs from the new copy with accumulation restarted, several
+    rounds alternate the two buffers, and a staged scene after a device refit carries the refitted tree."""
+    monkeypatch.delenv("CUDAPT_REFIT_HOST", raising=False)
+    scene = scenes.heightfield(n_quads=64)
+    v = scene[0]
+    tr = tracer(pt, scene, 192, 108)
+    tr.render(4)
+    ref = tr.read_accum()[0]
+    chk = tr.accel_checksum()
+    for k in range(3):
+        tr.reset()
+        tr.render(4)           # in flight ...
+        tr.stage_scene()       # ... while the next copy of the scene is uploaded
+        acc, fc = tr.read_accum()
+        assert fc == 4 and np.array_equal(bits(acc), bits(ref))
+        tr.render(4)           # swaps the buffers and restarts accumulation
+        acc, fc = tr.read_accum()
+        assert fc == 4 and np.array_equal(bits(acc), bits(ref))
+        assert tr.accel_checksum() == chk
+    tr.update_vertices(wobble(v, 1))
+    moved_chk = tr.accel_checksum()
+    tr.render(4)
+    moved = tr.read_accum()[0]
+    tr.stage_scene()           # staging is stale after the device refit: refreshed first
+    tr.render(4)
+    assert tr.accel_checksum() == moved_chk
+    assert np.array_equal(bits(tr.read_accum()[0]), bits(moved)) and not np.array_equal(bits(moved), bits(ref))
+    tr.stage_scene()
+    tr.update_vertices(v)      # a scene call commits the staged copy before it refits
+    tr.render(4)
+    assert np.array_equal(bits(tr.read_accum()[0]), bits(ref))
+    tr.close()
