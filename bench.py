@@ -199,6 +199,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
     ap.add_argument("--spp-pass", type=int, default=0, help="override samples per wavefront pass (debug)")
+    ap.add_argument("--partition", default="samples", choices=["samples", "tiles", "combined"],
+                    help="N > 1: how a step's work is split over the ranks (SURVEY 8e): sample ranges (B, default: best "
+                         "balance), interleaved 32x32 tiles (A: per-pixel sums in single-GPU order), or tile groups x "
+                         "sample ranges")
     ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],
                     help="N > 1 read-back tail: 'fused' = one reduce-scatter+resolve+gather kernel per rank over NVLink "
                          "peer memory (cudapt_reduce_resolve_peers); 'nccl' = NCCL reduce of the float buffer to rank 0")
@@ -246,8 +250,17 @@ def main():
     else:
         tr.upload_mesh(scene["v"], scene["t"], scene["m"], scene["mats"])
         scene_bytes = int(tr.stats().accel_bytes)
+    # Work split.  Every mode gives a rank W*H*spp paths per step; they differ in WHICH (pixel, frame) pairs.
+    #   samples : rank g renders frames g+1, g+1+G, ... of every pixel                      -> render(spp)
+    #   tiles   : rank g renders all G*spp frames of the 32x32 tiles it owns               -> render(spp * G)
+    #   combined: T tile ranks x G/T sample groups                                          -> render(spp * T)
+    tile_rank, tile_world, group, n_groups = part.layout(rank, world, args.partition)
+    frames_per_render = spp * tile_world
     if world > 1:
-        tr.set_frame_range(*part.frame_range(rank, world))  # sample-range sharding
+        if n_groups > 1:
+            tr.set_frame_range(*part.frame_range(group, n_groups))
+        if tile_world > 1:
+            tr.set_tile_partition(tile_rank, tile_world, 32, 32)
 
     stream = torch.cuda.ExternalStream(tr.stream_handle, device=local_rank)
     n_px = W * H
@@ -278,14 +291,14 @@ def main():
         with torch.cuda.stream(stream):
             if fused:
                 dist.all_reduce(tick)   # stream-ordered rendezvous: every rank's render is complete
-                tr.reduce_resolve_peers(peer_accum, rank, spp * world, root_rgba, None)  # image only: the merged floats stay distributed
+                tr.reduce_resolve_peers(peer_accum, rank, spp * world, root_rgba, None)  # spp * world frames per pixel in every mode; image only: the merged floats stay distributed
                 dist.all_reduce(tick)   # every rank's slice has landed in the root's buffers
             else:
                 part.reduce_accum(accum_t, dst=0)
 
     def step():
         tr.reset()
-        tr.render(spp)
+        tr.render(frames_per_render)
         tail()
 
     def sync_all():
@@ -353,7 +366,7 @@ def main():
             tr.upload_spheres(scene["spheres"])     # H2D of the step's scene; also restarts accumulation
         elif first:
             tr.reupload_scene()
-        tr.render(spp)
+        tr.render(frames_per_render)
         if wl["kind"] == "mesh" and not last:
             tr.stage_scene()                         # next step's scene: H2D concurrent with this step's rendering
         tail()
@@ -414,7 +427,8 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "name": wl["name"], "width": W, "height": H, "spp_per_gpu": spp,
                    "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
-                   "partition": ("one process per GPU; sample ranges per rank; " +
+                   "partition": ("one process per GPU; " + {"samples": "sample ranges per rank", "tiles": "interleaved 32x32 tiles per rank",
+                                                            "combined": f"{tile_world} tile ranks x {n_groups} sample groups"}[args.partition] + "; " +
                                  ("fused tail every step: one reduce-scatter + resolve + gather kernel per rank over "
                                   "NVLink peer memory (CUDA IPC), rank-ordered sums" if fused else
                                   "NCCL reduce(sum) of the float accumulation buffer to rank 0 at the end of every step"))

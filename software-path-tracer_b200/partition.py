@@ -37,3 +37,21 @@ def reduce_accum(accum, dst: int = 0):
 def total_frame_count(frames_per_rank: int, world: int, mode: str) -> int:
     """Samples per pixel held by the reduced buffer: sample ranges add up, tiles do not."""
     return frames_per_rank * world if mode == "frames" else frames_per_rank
+
+
+def layout(rank: int, world: int, mode: str):
+    """(tile_rank, tile_world, group, n_groups) of a rank: 'samples' = one sample range per rank,
+    'tiles' = one interleaved tile set per rank, 'combined' = tile ranks inside a group x sample ranges across groups
+    (4 tile ranks per group from 8 ranks up, else 2)."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} of {world}")
+    if world == 1 or mode == "samples":
+        return 0, 1, rank, world
+    if mode == "tiles":
+        return rank, world, 0, 1
+    if mode != "combined":
+        raise ValueError(mode)
+    tile_world = 4 if world % 4 == 0 and world > 4 else 2
+    if world % tile_world:
+        raise ValueError(f"combined partition needs a multiple of {tile_world} ranks")
+    return rank % tile_world, tile_world, rank // tile_world, world // tile_world

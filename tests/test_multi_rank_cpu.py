@@ -24,7 +24,12 @@ def _worker(rank, world, port, mode, out_path):
     scenes = importlib.import_module("software-path-tracer_b200.scenes")
     W, H, per = 64, 36, 3
     sph = scenes.app_spheres()
-    if mode == "frames":
+    if mode == "combined":  # bench.py --partition combined: tile ranks inside a group x sample ranges across groups
+        tile_rank, tile_world, group, n_groups = part.layout(rank, world, "combined")
+        first, stride = part.frame_range(group, n_groups)
+        p = oracle.twin_params(W, H, threads=1, part_rank=tile_rank, part_world=tile_world, tile_w=16, tile_h=8)
+        acc, _, _, _ = oracle.twin_render_spheres(p, sph, per, first_frame=first, frame_stride=stride)
+    elif mode == "frames":
         first, stride = part.frame_range(rank, world)
         p = oracle.twin_params(W, H, threads=1)
         acc, _, _, _ = oracle.twin_render_spheres(p, sph, per, first_frame=first, frame_stride=stride)
@@ -41,7 +46,7 @@ def _worker(rank, world, port, mode, out_path):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,mode", [(2, "frames"), (2, "tiles"), (3, "tiles")])
+@pytest.mark.parametrize("world,mode", [(2, "frames"), (2, "tiles"), (3, "tiles"), (4, "combined")])
 def test_reduce_of_rank_shares_matches_single_rank(tmp_path, oracle, scenes, world, mode):
     out = str(tmp_path / "acc.npy")
     port = 29500 + (os.getpid() % 2000) + world
@@ -49,13 +54,26 @@ def test_reduce_of_rank_shares_matches_single_rank(tmp_path, oracle, scenes, wor
     got = np.load(out)
     part = importlib.import_module("software-path-tracer_b200.partition")
     W, H, per = 64, 36, 3
-    n = part.total_frame_count(per, world, mode)
+    n = per * 2 if mode == "combined" else part.total_frame_count(per, world, mode)  # 4 ranks = 2 tile ranks x 2 groups
     want, _, _, _ = oracle.twin_render_spheres(oracle.twin_params(W, H, threads=1), scenes.app_spheres(), n)
     assert np.all(got[..., 3] == n)
     if mode == "tiles":
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32))  # bit-identical: x + 0 = x
     else:
         assert np.allclose(got, want, rtol=1e-6, atol=1e-5)  # float re-association only
+
+
+def test_layouts_cover_every_pixel_frame_pair_once():
+    part = importlib.import_module("software-path-tracer_b200.partition")
+    for world in (1, 2, 4, 8):
+        for mode in ("samples", "tiles", "combined"):
+            seen = {}
+            for r in range(world):
+                tr_, tw, g, ng = part.layout(r, world, mode)
+                assert 0 <= tr_ < tw and 0 <= g < ng and tw * ng == world
+                seen[(tr_, g)] = seen.get((tr_, g), 0) + 1
+            assert len(seen) == world and set(seen.values()) == {1}
+    assert part.layout(5, 8, "combined") == (1, 4, 1, 2) and part.layout(3, 4, "combined") == (1, 2, 1, 2)
 
 
 def test_frame_ranges_partition_the_frames():
