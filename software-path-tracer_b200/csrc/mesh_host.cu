@@ -365,8 +365,9 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   const uint32_t n_pixels = a.im.width * a.im.height;
   uint32_t S = std::max(1u, std::min(a.samples_per_pass, a.n_frames));
   // 148 B of state + queues per path: keep a pass within 3/4 of the memory that is free (or already ours), and its
-  // path ids within 32 bits
-  {
+  // path ids within 32 bits.  The driver is asked only when the state would have to GROW: cudaMemGetInfo can take
+  // milliseconds, and it sits between the render's first event and its first kernel.
+  if ((uint64_t)n_pixels * S > dev_->state_paths) {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
       const size_t ours = (size_t)dev_->state_paths * 148u;
