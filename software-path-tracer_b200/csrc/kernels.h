@@ -95,6 +95,8 @@ struct PassParams {
   uint32_t n_pixels;
   uint32_t samples;          // samples of every pixel in this pass
   uint32_t chunked;          // path id layout, see path_id()
+  uint32_t n_slots;          // chunked layout: pixel slots = 8x8 tiles covering the image, >= n_pixels
+  uint32_t slot_tiles_x;
   uint32_t first_frame;      // global 1-based frame index of sample 0 of this pass
   uint32_t frame_stride;
   float4* accum;
@@ -105,19 +107,37 @@ struct PassParams {
 
 // PATH ID of (pixel, sample-in-pass).  Sample-major (id = s * n_pixels + pixel: a warp of consecutive ids = 32
 // neighbouring pixels) or, when the camera rays are traced as packets (primary_packet.cu: one warp = 32 samples of a
-// pixel), CHUNKED: id = ((s / 32) * n_pixels + pixel) * 32 + s % 32, so that a packet's state is contiguous.
-__host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
-  return p.chunked ? (((s >> 5) * p.n_pixels + pixel) << 5) | (s & 31u) : s * p.n_pixels + pixel;
+// pixel), CHUNKED: id = ((s / 32) * n_slots + slot) * 32 + s % 32, so that a packet's state is contiguous.  `slot`
+// numbers the pixels tile by tile (8x8 tiles, row-major inside a tile; the tile grid is padded to the image, slots
+// outside it are skipped): consecutive packets, and with them consecutive entries of the bounce-1 queue, come from a
+// compact 2-D neighbourhood of the image instead of a scanline, which is what the caches of the per-ray kernel want.
+__host__ __device__ inline uint32_t pixel_slot(const PassParams& p, uint32_t x, uint32_t y) {
+  return (((y >> 3) * p.slot_tiles_x + (x >> 3)) << 6) | ((y & 7u) << 3) | (x & 7u);
 }
-__host__ __device__ inline void path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
+__host__ __device__ inline bool slot_pixel(const PassParams& p, uint32_t g, uint32_t& x, uint32_t& y) {
+  const uint32_t tile = g >> 6, ty = tile / p.slot_tiles_x, tx = tile - ty * p.slot_tiles_x;
+  x = (tx << 3) | (g & 7u);
+  y = (ty << 3) | ((g >> 3) & 7u);
+  return x < p.im.width && y < p.im.height;
+}
+__host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
+  if (!p.chunked) return s * p.n_pixels + pixel;
+  const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
+  return (((s >> 5) * p.n_slots + pixel_slot(p, x, y)) << 5) | (s & 31u);
+}
+// false: the id is a padding slot of the chunked layout (no pixel)
+__host__ __device__ inline bool path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
   if (p.chunked) {
-    const uint32_t g = id >> 5, chunk = g / p.n_pixels;
-    pixel = g - chunk * p.n_pixels;
+    const uint32_t gg = id >> 5, chunk = gg / p.n_slots;
+    uint32_t x, y;
+    const bool ok = slot_pixel(p, gg - chunk * p.n_slots, x, y);
+    pixel = y * p.im.width + x;
     s = (chunk << 5) | (id & 31u);
-  } else {
-    s = id / p.n_pixels;
-    pixel = id - s * p.n_pixels;
+    return ok;
   }
+  s = id / p.n_pixels;
+  pixel = id - s * p.n_pixels;
+  return true;
 }
 
 constexpr int kTraceBlock = 128;

@@ -363,22 +363,24 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     return cudaErrorInvalidValue;
   }
   const uint32_t n_pixels = a.im.width * a.im.height;
+  // pixel slots of the chunked path-id layout (kernels.h): the image padded to 8x8 tiles
+  const uint32_t slot_tiles_x = (a.im.width + 7u) / 8u, n_slots = slot_tiles_x * ((a.im.height + 7u) / 8u) * 64u;
   uint32_t S = std::max(1u, std::min(a.samples_per_pass, a.n_frames));
   // 148 B of state + queues per path: keep a pass within 3/4 of the memory that is free (or already ours), and its
   // path ids within 32 bits.  The driver is asked only when the state would have to GROW: cudaMemGetInfo can take
   // milliseconds, and it sits between the render's first event and its first kernel.
-  if ((uint64_t)n_pixels * S > dev_->state_paths) {
+  if ((uint64_t)n_slots * S > dev_->state_paths) {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
       const size_t ours = (size_t)dev_->state_paths * 148u;
       const size_t budget = (free_b + ours) / 4u * 3u;
-      const size_t fit = budget / ((size_t)n_pixels * 148u);
+      const size_t fit = budget / ((size_t)n_slots * 148u);
       S = (uint32_t)std::max<size_t>(1, std::min<size_t>(S, fit));
     }
-    S = (uint32_t)std::min<uint64_t>(S, 0xFFFFFFFFull / n_pixels);
+    S = (uint32_t)std::min<uint64_t>(S, 0xFFFFFFFFull / n_slots);
   }
   const uint32_t max_b = (uint32_t)a.ip.max_bounces;
-  cudaError_t e = ensure_state(dev_, n_pixels * S, max_b);
+  cudaError_t e = ensure_state(dev_, n_slots * S, max_b);
   if (e != cudaSuccess) {
     *err = "wavefront state allocation";
     return e;
@@ -395,6 +397,8 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   p.im = a.im;
   p.ip = a.ip;
   p.n_pixels = n_pixels;
+  p.n_slots = n_slots;
+  p.slot_tiles_x = slot_tiles_x;
   p.frame_stride = a.frame_stride;
   p.accum = a.accum;
   p.counters = a.counters;

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   const PassParams& p = a.p;
   const unsigned lane = threadIdx.x & 31u;
   const uint32_t n_warps = gridDim.x * kPacketWarps;
-  const uint32_t n_tasks = p.n_pixels * (p.samples / (32u * kRays));
+  const uint32_t n_tasks = p.n_slots * (p.samples / (32u * kRays));
   const int ax_k = a.axis_k, ax_a = (ax_k + 1) % 3, ax_b = (ax_k + 2) % 3;
   const float sigma = a.sigma;
   const f3 O = p.cam.origin;
@@ -123,12 +123,13 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0;
 
   for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) {
-    const uint32_t chunk = task / p.n_pixels, pixel = task - chunk * p.n_pixels;
-    const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
-    if (!owns_pixel(p.im, x, y)) continue;  // warp-uniform
+    const uint32_t chunk = task / p.n_slots, slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
+    uint32_t x, y;
+    if (!slot_pixel(p, slot, x, y) || !owns_pixel(p.im, x, y)) continue;  // warp-uniform
+    const uint32_t pixel = y * p.im.width + x;
     // ---- the 32 * kRays rays (K1); ray j of a lane is sample 32 * (chunk * kRays + j) + lane ----
-    const uint32_t id0 = ((chunk * kRays) * p.n_pixels + pixel) * 32u + lane;  // chunked path id (kernels.h path_id())
-    const uint32_t id_step = p.n_pixels * 32u;                                 // to the same lane of the next chunk
+    const uint32_t id0 = ((chunk * kRays) * p.n_slots + slot) * 32u + lane;  // chunked path id (kernels.h path_id())
+    const uint32_t id_step = p.n_slots * 32u;                                // to the same lane of the next chunk
     f3 dir[kRays];
     float w[kRays];  // depth per unit t
     uint32_t ku_min = 0xFFFFFFFFu, ku_max = 0u, kv_min = 0xFFFFFFFFu, kv_max = 0u;
@@ -291,7 +292,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       if (kCount) ++n_bail;
     }
   }
-  if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_pixels * p.samples;
+  if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
   const uint64_t wr = warp_sum_u32(done_rays);
   if (lane == 0 && wr) {
     atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
@@ -335,7 +336,7 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
   const uint32_t chunks = p.samples / 32u;
   int rays = re ? atoi(re) : 4;
   rays = rays >= 4 && chunks % 4u == 0u ? 4 : (rays >= 2 && chunks % 2u == 0u ? 2 : 1);
-  const uint32_t n_tasks = p.n_pixels * (chunks / (uint32_t)rays);
+  const uint32_t n_tasks = p.n_slots * (chunks / (uint32_t)rays);
   const uint32_t warps_per_cta = kPacketWarps;
   uint32_t grid = (uint32_t)sm_count * (rays == 1 ? 8u : (rays == 2 ? 6u : 4u));
   const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;

@@ -156,9 +156,8 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
     path_1 = path_2;
     path_2 = (k + 2 < rounds && i + 2 * stride < n) ? (ident ? i + 2 * stride : qin[i + 2 * stride]) : 0u;
     if (k + 1 < rounds) hit_1 = st.hit[path_1];  // path_1 was loaded a round ago: no stall here
-    if (i < n) {
-      uint32_t s, pixel;
-      path_decode(p, path, pixel, s);
+    uint32_t s = 0, pixel = 0;
+    if (i < n && path_decode(p, path, pixel, s)) {
       const uint32_t frame = p.first_frame + s * p.frame_stride;
       const float t = __uint_as_float(h.x);
       const float4 o4 = camera_implied ? make_float4(p.cam.origin.x, p.cam.origin.y, p.cam.origin.z, p.ip.tnear) : st.ray_o[path];
