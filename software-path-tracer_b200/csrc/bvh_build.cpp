@@ -47,6 +47,7 @@ struct Node2 {
   Box box;
   uint32_t left = 0, right = 0;   // children (internal)
   uint32_t first = 0, count = 0;  // leaf: range in the permutation
+  uint32_t total = 0;             // every node: triangles below it = perm[first .. first + total)
 };
 
 struct Builder {
@@ -68,6 +69,8 @@ struct Builder {
       cbox.grow(cen + 3 * p, cen + 3 * p);
     }
     nodes[node].box = box;
+    nodes[node].first = begin;
+    nodes[node].total = end - begin;
     const uint32_t count = end - begin;
     auto make_leaf = [&]() {
       nodes[node].first = begin;
@@ -152,6 +155,71 @@ struct Child {
   bool leaf;
 };
 
+// Optimal collapse of the binary tree into 8-wide nodes (the dynamic programme of Ylitie, Karras & Laine, HPG 2017,
+// section 3.1): c[i] = cheapest SAH cost of representing the subtree of a binary node as a forest of at most i roots,
+// each a leaf (<= leaf_max triangles) or an 8-wide node.  The greedy "open the largest child" collapse leaves the nodes
+// 4.5/8 full (78 % of them leaf-only with ~3.5 leaves); this one 6.2/8.  Opt-in, see build_bvh8().
+struct Collapse {
+  float c[8];       // [1..7]
+  uint8_t k[9];     // [2..7]: triangles^W roots given to the left child when the forest of i roots is split (0: same as i-1); [8]: the split of the 8-wide node
+  uint8_t leaf1;    // the single-root form is a leaf (else an 8-wide node)
+};
+
+void collapse_costs(const std::vector<Node2>& n2, uint32_t n_used, uint32_t leaf_max, float c_node, float c_prim,
+                    std::vector<Collapse>* out) {
+  out->assign(n_used, Collapse{});
+  for (uint32_t n = n_used; n-- > 0;) {  // children have larger indices than their parent
+    const Node2& N = n2[n];
+    Collapse& R = (*out)[n];
+    const float A = N.box.area();
+    if (N.count) {
+      for (int i = 1; i <= 7; ++i) R.c[i] = A * (float)N.count * c_prim;
+      R.leaf1 = 1;
+      continue;
+    }
+    const Collapse &L = (*out)[N.left], &Rt = (*out)[N.right];
+    float D[9];
+    uint8_t kD[9];
+    for (int j = 2; j <= 8; ++j) {
+      D[j] = kInf;
+      kD[j] = 0;
+      for (int k = std::max(1, j - 7); k <= std::min(7, j - 1); ++k) {
+        const float v = L.c[k] + Rt.c[j - k];
+        if (v < D[j]) D[j] = v, kD[j] = (uint8_t)k;
+      }
+    }
+    const float c_leaf = N.total <= leaf_max ? A * (float)N.total * c_prim : kInf;
+    const float c_int = D[8] + A * c_node;
+    R.leaf1 = c_leaf <= c_int;
+    R.c[1] = R.leaf1 ? c_leaf : c_int;
+    R.k[8] = kD[8];
+    for (int i = 2; i <= 7; ++i) {
+      if (D[i] < R.c[i - 1]) {
+        R.c[i] = D[i];
+        R.k[i] = kD[i];
+      } else {
+        R.c[i] = R.c[i - 1];
+        R.k[i] = 0;
+      }
+    }
+  }
+}
+
+void collect_roots(const std::vector<Node2>& n2, const std::vector<Collapse>& dp, uint32_t m, int i, std::vector<Child>* ch) {
+  const Node2& M = n2[m];
+  if (M.count) {
+    ch->push_back({m, M.box, true});
+    return;
+  }
+  while (i > 1 && dp[m].k[i] == 0) --i;
+  if (i == 1) {
+    ch->push_back({m, M.box, dp[m].leaf1 != 0});
+    return;
+  }
+  collect_roots(n2, dp, M.left, dp[m].k[i], ch);
+  collect_roots(n2, dp, M.right, i - dp[m].k[i], ch);
+}
+
 // Step 4 of the build and the triangle packing live in bvh8_refit.h (shared with the GPU refit kernels).
 void quantise_node(const Box& nb, const Box* slot_box, const bool* slot_used, Bvh8Node* N) {
   Box3 b3, sb[8];
@@ -208,6 +276,18 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
   for (int k = 0; k < 3; ++k) out->world_lo[k] = n2[0].box.lo[k], out->world_hi[k] = n2[0].box.hi[k];
   const double root_area = std::max((double)n2[0].box.area(), 1e-30);
 
+  // CUDAPT_BVH_COLLAPSE=optimal selects the dynamic-programming collapse: 33 % fewer nodes and 4.5 % fewer node steps
+  // per ray, but 2 % more triangle tests, which cost this traversal more (profiles/r01_notes.md: C3 step 19.94 vs
+  // 19.95 ms, C4 88.5 vs 89.2 ms) -- the greedy collapse stays the default
+  const char* ce = std::getenv("CUDAPT_BVH_COLLAPSE");
+  const bool optimal = ce && std::string(ce) == "optimal";
+  std::vector<Collapse> dp;
+  if (optimal) {
+    float c_node = 1.0f, c_prim = 1.0f;
+    if (const char* e = std::getenv("CUDAPT_BVH_NODE_COST")) c_node = (float)std::atof(e);
+    if (const char* e = std::getenv("CUDAPT_BVH_PRIM_COST")) c_prim = (float)std::atof(e);
+    collapse_costs(n2, B.next.load(), B.leaf_max, c_node, c_prim, &dp);
+  }
   struct Work {
     uint32_t node2, node8, depth;
   };
@@ -220,8 +300,11 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
     out->max_depth = std::max(out->max_depth, w.depth);
     if (out->level_start.size() < w.depth) out->level_start.push_back(w.node8);  // breadth-first: first node of the level
     std::vector<Child> ch;
-    if (n2[w.node2].count) {
+    if (n2[w.node2].count || (optimal && dp[w.node2].leaf1)) {
       ch.push_back({w.node2, n2[w.node2].box, true});  // whole scene is one leaf
+    } else if (optimal) {
+      collect_roots(n2, dp, n2[w.node2].left, dp[w.node2].k[8], &ch);
+      collect_roots(n2, dp, n2[w.node2].right, 8 - dp[w.node2].k[8], &ch);
     } else {
       ch.push_back({n2[w.node2].left, n2[n2[w.node2].left].box, n2[n2[w.node2].left].count != 0});
       ch.push_back({n2[w.node2].right, n2[n2[w.node2].right].box, n2[n2[w.node2].right].count != 0});
@@ -297,7 +380,7 @@ bool build_bvh8(const float* vertices, uint32_t nv, const uint32_t* indices, uin
         N.imask |= (uint8_t)(1u << s);
         queue.push_back({ch[i].node2, next_internal++, w.depth + 1});
       } else {
-        const uint32_t cnt = n2[ch[i].node2].count;  // 1..3
+        const uint32_t cnt = n2[ch[i].node2].total;  // 1..3 (a leaf of the binary tree, or a subtree the collapse merged)
         for (uint32_t j = 0; j < cnt; ++j) N.tri_valid |= 1u << (8 * j + s);
       }
     }

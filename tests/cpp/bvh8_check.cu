@@ -154,6 +154,19 @@ static int check(const char* name, Scene sc, int n_rays, bool from_inside, bool 
       if (occ.tri != 0xFFFFFFFFu && want.t * 0.99f > tnear) ++bad;
     }
   }
+  if (std::getenv("BVH8_CHECK_STATS")) {  // slot usage of the tree (builder tuning)
+    size_t internal = 0, leaf_slots = 0, leaf_tris = 0, leaf_only_nodes = 0;
+    for (const Bvh8Node& N : bvh.nodes) {
+      internal += (size_t)__builtin_popcount(N.imask);
+      const uint32_t slots = (N.tri_valid | (N.tri_valid >> 8) | (N.tri_valid >> 16)) & 0xFFu;
+      leaf_slots += (size_t)__builtin_popcount(slots);
+      leaf_tris += (size_t)__builtin_popcount(N.tri_valid);
+      if (!N.imask) ++leaf_only_nodes;
+    }
+    std::printf("%s: per node: %.2f internal children, %.2f leaf slots, %.2f triangles (%.2f per leaf slot); %.1f %% of the nodes have only leaves\n",
+                name, (double)internal / bvh.nodes.size(), (double)leaf_slots / bvh.nodes.size(), (double)leaf_tris / bvh.nodes.size(),
+                (double)leaf_tris / leaf_slots, 100.0 * leaf_only_nodes / bvh.nodes.size());
+  }
   std::printf("%s: tris %u nodes %zu depth %u sah %.2f | rays %d hits %d mismatches %d | nodes/ray %.2f tris/ray %.2f max stack %d\n",
               name, nt, bvh.nodes.size(), bvh.max_depth, bvh.sah_cost, n_rays, hits, bad, nodes_per_ray / n_rays,
               tris_per_ray / n_rays, max_sp);
