@@ -208,8 +208,9 @@ int cudapt_set_postprocess(cudapt_ctx* ctx, const cudapt_postprocess* pp);
 /* The exposure multiplier the last cudapt_resolve_rgba8 used (the auto-exposure result when enabled). */
 int cudapt_get_exposure(cudapt_ctx* ctx, float* exposure);
 /* Image writer for headless use (the reference only displays through SDL, App.cpp:236-238):
- * ".ppm" = binary P6 of the post-processed 8-bit image, ".pfm" = float RGB accum/frame_count (bottom row first,
- * little endian), chosen by the file extension. */
+ * ".png" = 8-bit RGBA and ".ppm" = binary P6 of the post-processed image, ".pfm" = float RGB accum/frame_count
+ * (bottom row first, little endian), chosen by the file extension.  The PNG is written without a compression
+ * library (stored deflate blocks). */
 int cudapt_write_image(cudapt_ctx* ctx, const char* path);
 
 /* Float accumulation (private m_accumulation_buffer, CPT.h:72): 4*W*H floats RGBA, and the frame count. */

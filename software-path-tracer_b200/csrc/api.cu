@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -593,13 +594,90 @@ int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
   return CUDAPT_OK;
 }
 
+// PNG, 8-bit RGBA, written without a compression library: the zlib stream consists of STORED deflate blocks (RFC 1951
+// 3.2.4), which every PNG reader accepts; CRC-32 per chunk (PNG spec 5.5), Adler-32 over the filtered scanlines.
+namespace {
+uint32_t crc32_update(uint32_t crc, const unsigned char* p, size_t n) {
+  static uint32_t table[256];
+  static bool ready = false;
+  if (!ready) {
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+      table[i] = c;
+    }
+    ready = true;
+  }
+  for (size_t i = 0; i < n; ++i) crc = table[(crc ^ p[i]) & 0xFFu] ^ (crc >> 8);
+  return crc;
+}
+void put_be32(std::vector<unsigned char>& v, uint32_t x) {
+  v.push_back((unsigned char)(x >> 24)), v.push_back((unsigned char)(x >> 16)), v.push_back((unsigned char)(x >> 8)), v.push_back((unsigned char)x);
+}
+void put_chunk(std::vector<unsigned char>& out, const char* type, const std::vector<unsigned char>& data) {
+  put_be32(out, (uint32_t)data.size());
+  const size_t start = out.size();
+  out.insert(out.end(), type, type + 4);
+  out.insert(out.end(), data.begin(), data.end());
+  put_be32(out, crc32_update(0xFFFFFFFFu, out.data() + start, out.size() - start) ^ 0xFFFFFFFFu);
+}
+std::vector<unsigned char> encode_png_rgba8(const uint32_t* packed, uint32_t W, uint32_t H) {
+  // filtered scanlines: filter byte 0 + R G B A per pixel (packed word = R<<24 | G<<16 | B<<8 | A, Color.h:9)
+  std::vector<unsigned char> raw((size_t)H * (1 + 4 * (size_t)W));
+  size_t o = 0;
+  for (uint32_t y = 0; y < H; ++y) {
+    raw[o++] = 0;
+    for (uint32_t x = 0; x < W; ++x) {
+      const uint32_t p = packed[(size_t)y * W + x];
+      raw[o++] = (unsigned char)(p >> 24), raw[o++] = (unsigned char)(p >> 16), raw[o++] = (unsigned char)(p >> 8), raw[o++] = (unsigned char)p;
+    }
+  }
+  std::vector<unsigned char> z;
+  z.push_back(0x78), z.push_back(0x01);  // zlib header: deflate, 32 K window, no preset dictionary
+  uint32_t a = 1, b = 0;
+  for (size_t pos = 0; pos < raw.size() || pos == 0;) {
+    const size_t n = std::min<size_t>(65535, raw.size() - pos);
+    z.push_back(pos + n >= raw.size() ? 1 : 0);  // BFINAL, BTYPE = 00 (stored)
+    z.push_back((unsigned char)(n & 0xFF)), z.push_back((unsigned char)(n >> 8));
+    z.push_back((unsigned char)(~n & 0xFF)), z.push_back((unsigned char)((~n >> 8) & 0xFF));
+    z.insert(z.end(), raw.begin() + pos, raw.begin() + pos + n);
+    for (size_t i = pos; i < pos + n; ++i) {
+      a = (a + raw[i]) % 65521u;
+      b = (b + a) % 65521u;
+    }
+    pos += n;
+    if (n == 0) break;
+  }
+  put_be32(z, (b << 16) | a);
+  std::vector<unsigned char> out = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+  std::vector<unsigned char> ihdr;
+  put_be32(ihdr, W), put_be32(ihdr, H);
+  ihdr.push_back(8), ihdr.push_back(6), ihdr.push_back(0), ihdr.push_back(0), ihdr.push_back(0);  // 8 bit, RGBA, no interlace
+  put_chunk(out, "IHDR", ihdr);
+  put_chunk(out, "IDAT", z);
+  put_chunk(out, "IEND", {});
+  return out;
+}
+}  // namespace
+
 int cudapt_write_image(cudapt_ctx* ctx, const char* path) {
   if (!ctx || !path) return CUDAPT_ERR_INVALID;
   const size_t len = std::strlen(path);
   const bool ppm = len > 4 && std::strcmp(path + len - 4, ".ppm") == 0;
   const bool pfm = len > 4 && std::strcmp(path + len - 4, ".pfm") == 0;
-  if (!ppm && !pfm) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: '%s' is neither .ppm nor .pfm", path);
+  const bool png = len > 4 && std::strcmp(path + len - 4, ".png") == 0;
+  if (!ppm && !pfm && !png) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: '%s' is neither .png, .ppm nor .pfm", path);
   const uint32_t W = ctx->width, H = ctx->height;
+  if (png) {
+    const int rc = resolve_to_pinned(ctx, "cudapt_write_image");
+    if (rc != CUDAPT_OK) return rc;
+    const std::vector<unsigned char> bytes = encode_png_rgba8(ctx->h_pinned_rgba, W, H);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: cannot open '%s'", path);
+    const bool ok = std::fwrite(bytes.data(), 1, bytes.size(), f) == bytes.size();
+    std::fclose(f);
+    return ok ? CUDAPT_OK : fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: short write to '%s'", path);
+  }
   if (ppm) {
     const int rc = resolve_to_pinned(ctx, "cudapt_write_image");
     if (rc != CUDAPT_OK) return rc;

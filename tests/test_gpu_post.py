@@ -87,8 +87,28 @@ def test_image_writer(pt, oracle, rendered, tmp_path):
     assert raw.startswith(head) and len(raw) == len(head) + 12 * W * H
     img = np.frombuffer(raw[len(head):], "<f4").reshape(H, W, 3)[::-1]  # bottom row first
     assert np.array_equal(img.view(np.uint32), (acc[..., :3] / np.float32(N)).view(np.uint32))
+    # PNG: decoded with nothing but zlib + struct (stored deflate blocks, CRC-32 per chunk, filter 0 scanlines)
+    import struct, zlib
+    png = str(tmp_path / "out.png")
+    tr.write_image(png)
+    raw = open(png, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        data = raw[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])
+        assert crc == (zlib.crc32(typ + data) & 0xFFFFFFFF)
+        chunks.append((typ, data))
+        pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (W, H, 8, 6, 0, 0, 0)
+    lines = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(H, 1 + 4 * W)
+    assert not lines[:, 0].any()
+    rgba = lines[:, 1:].reshape(H, W, 4)
+    assert np.array_equal(rgba[..., :3].astype(np.int32), want) and np.all(rgba[..., 3] == 255)
     with pytest.raises(pt.CudaptError):
-        tr.write_image(str(tmp_path / "out.png"))
+        tr.write_image(str(tmp_path / "out.exr"))
     tr.set_postprocess(pt.default_postprocess())
 
 
