@@ -51,3 +51,10 @@ def scenes(built):
 def golden():
     import numpy as np
     return np.load(os.path.join(ROOT, "tests", "golden", "c1_spheres_96x54.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_mesh():
+    """Twin-generated (tests/golden/make_golden_mesh.py): freezes the mesh specification; not pinned by the reference."""
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "c2_cornell_64x36.npz"))

@@ -216,3 +216,31 @@ def test_update_vertices_refit_equals_fresh_build(pt, oracle, scenes):
     assert same_frac(before, refit) < 0.9
     want, _, _, _ = oracle.TwinMesh(v2, t, m, mats).render(oracle.twin_params(W, H, rng_mode=1, **kw), N)
     assert same_frac(refit, want) >= 0.999
+
+
+def test_mesh_golden_fixture(pt, golden_mesh):
+    """GPU vs the COMMITTED mesh vectors (tests/golden/c2_cornell_64x36.npz, generated by the twin): per-ray kernel
+    (4 spp, passes of 2), packet path (one 32-sample pass) and the thin lens."""
+    g = golden_mesh
+    W, H = int(g["width"]), int(g["height"])
+    kw = dict(rng_mode=1, max_bounces=6, jitter=1, nee=1, sky_scale=0.0, seed=17)
+
+    def run(n, spp_pass, **cam):
+        with pt.PathTracer(pt.default_config(samples_per_pass=spp_pass, **kw)) as tr:
+            tr.set_camera(pt.default_camera(tan_half_fov=0.36, **cam))
+            tr.set_resolution(W, H)
+            tr.upload_mesh(g["vertices"], g["triangles"], g["material_id"], g["materials"])
+            tr.render(n)
+            acc, _ = tr.read_accum()
+            prim, t = tr.read_primary_hits()
+            st = tr.stats()
+        return acc, prim, t, st
+
+    acc, prim, t, st = run(4, 2)
+    got = np.where(prim == 0xFFFFFFFF, -1, prim.astype(np.int64))
+    assert np.array_equal(got, g["primary_idx"]) and np.array_equal(bits(t), bits(g["primary_t"]))
+    assert same_frac(acc, g["accum4"]) >= 0.999 and abs(int(st.rays) - int(g["rays4"])) <= 0.002 * int(g["rays4"])
+    acc, _, _, st = run(32, 32)
+    assert st.packet_rays > 0 and same_frac(acc, g["accum32"]) >= 0.999
+    acc, _, _, st = run(32, 32, lens_radius=0.05, focus_distance=4.0)
+    assert st.packet_rays == 0 and same_frac(acc, g["accum32_lens"]) >= 0.999

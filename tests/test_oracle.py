@@ -25,6 +25,25 @@ def test_twin_matches_golden_bit_for_bit(oracle, golden):
     assert np.array_equal(oracle.twin_resolve_rgba8(golden["accum4"], 4), golden["rgba4"])
 
 
+MESH_KW = dict(rng_mode=1, max_bounces=6, jitter=1, nee=1, sky_scale=0.0, seed=17, cam_tan_half_fov=0.36)
+
+
+def test_twin_mesh_matches_committed_vectors(oracle, golden_mesh):
+    """The twin's mesh integrator (triangles, materials, NEE, Philox, thin lens) reproduces the committed fixture bit
+    for bit: a change of the mesh specification cannot slip in unnoticed.  (Twin-generated: parity unpinned by the
+    reference, which has no triangle path.)"""
+    g = golden_mesh
+    W, H = int(g["width"]), int(g["height"])
+    mesh = oracle.TwinMesh(g["vertices"], g["triangles"], g["material_id"], g["materials"])
+    acc, idx, t, c = mesh.render(oracle.twin_params(W, H, **MESH_KW), 4, want_primary=True)
+    assert np.array_equal(bits(acc), bits(g["accum4"])) and c.rays == int(g["rays4"])
+    assert np.array_equal(idx, g["primary_idx"]) and np.array_equal(bits(t), bits(g["primary_t"]))
+    acc, _, _, c = mesh.render(oracle.twin_params(W, H, **MESH_KW), 32)
+    assert np.array_equal(bits(acc), bits(g["accum32"])) and c.rays == int(g["rays32"])
+    acc, _, _, _ = mesh.render(oracle.twin_params(W, H, cam_lens_radius=0.05, cam_focus_distance=4.0, **MESH_KW), 32)
+    assert np.array_equal(bits(acc), bits(g["accum32_lens"]))
+
+
 def test_reference_matches_golden(oracle, golden):
     """Tier 1 rebuilt now reproduces the committed fixture (guards compiler/flag drift)."""
     if not oracle.ref_available():
