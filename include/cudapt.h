@@ -144,6 +144,11 @@ int cudapt_upload_mesh(cudapt_ctx* ctx, const float* vertices, uint32_t nv, cons
 int cudapt_upload_materials(cudapt_ctx* ctx, const cudapt_material* materials, uint32_t n);
 /* Builds the 8-wide quantised BVH on the host (SAH) and uploads it; replaces rtcCommitScene (CPT.cpp:403). */
 int cudapt_build_accel(cudapt_ctx* ctx);
+/* The same, built ON THE DEVICE (csrc/lbvh_build.cu: Morton codes, radix sort, binary radix tree, collapse to 8-wide
+ * nodes, quantisation by the refit kernels): milliseconds instead of the host builder's fraction of a second per
+ * million triangles, for scenes whose topology changes (SURVEY.md 8f-3 "refit / rebuild"); the tree is of lower
+ * quality (no SAH), images are identical.  Needs at least two triangles. */
+int cudapt_build_accel_device(cudapt_ctx* ctx);
 /* Copies the already built scene (BVH nodes, packed triangles, materials, light list) from the library's
  * pinned host staging to the device again and restarts accumulation -- the per-frame cost of a scene that
  * changed on the host without changing topology (the reference re-commits its Embree scene whenever

@@ -73,7 +73,7 @@ EXPORTS = [
     "cudapt_default_config", "cudapt_default_camera", "cudapt_camera_look_at", "cudapt_create", "cudapt_destroy", "cudapt_last_error",
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
-    "cudapt_reupload_scene", "cudapt_stage_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
+    "cudapt_build_accel_device", "cudapt_reupload_scene", "cudapt_stage_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
     "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
@@ -116,6 +116,7 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_upload_mesh.argtypes = [vp, vp, u32, vp, u32, vp]
     lib.cudapt_upload_materials.argtypes = [vp, vp, u32]
     lib.cudapt_build_accel.argtypes = [vp]
+    lib.cudapt_build_accel_device.argtypes = [vp]
     lib.cudapt_reupload_scene.argtypes = [vp]
     lib.cudapt_stage_scene.argtypes = [vp]
     lib.cudapt_update_vertices.argtypes = [vp, vp, u32]
@@ -251,7 +252,7 @@ class PathTracer:
         ids = None if node_id is None else np.ascontiguousarray(node_id, np.uint32)
         self._chk(self._lib.cudapt_upload_spheres(self._h, _p(s), _p(ids), len(s)))
 
-    def upload_mesh(self, vertices, indices, material_id=None, materials=None, build=True):
+    def upload_mesh(self, vertices, indices, material_id=None, materials=None, build=True, device_build=False):
         v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
         i = np.ascontiguousarray(indices, np.uint32).reshape(-1, 3)
         m = None if material_id is None else np.ascontiguousarray(material_id, np.uint32)
@@ -260,10 +261,14 @@ class PathTracer:
             mats = np.ascontiguousarray(materials, MATERIAL_DTYPE)
             self._chk(self._lib.cudapt_upload_materials(self._h, _p(mats), len(mats)))
         if build:
-            self.build_accel()
+            self.build_accel_device() if device_build else self.build_accel()
 
     def build_accel(self):
         self._chk(self._lib.cudapt_build_accel(self._h))
+
+    def build_accel_device(self):
+        """BVH build on the GPU (linear BVH): fast, lower tree quality, identical images."""
+        self._chk(self._lib.cudapt_build_accel_device(self._h))
 
     def update_vertices(self, vertices):
         v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)

@@ -388,6 +388,20 @@ int cudapt_build_accel(cudapt_ctx* ctx) {
   return restart_accumulation(ctx);
 }
 
+int cudapt_build_accel_device(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->mesh.has_host_mesh()) return fail(ctx, CUDAPT_ERR_NO_SCENE, "cudapt_build_accel_device: no mesh uploaded");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::string err;
+  uint64_t launches = 0;
+  const bool ok = ctx->mesh.build_on_device(ctx->stream, &launches, &err);
+  ctx->launches += launches;
+  if (!ok) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_build_accel_device: %s", err.c_str());
+  ctx->scene = cudapt_ctx::kMesh;
+  return restart_accumulation(ctx);
+}
+
 // a staged scene (cudapt_stage_scene) takes effect before anything else touches the scene
 static int commit_staged_scene(cudapt_ctx* ctx) {
   if (ctx->scene != cudapt_ctx::kMesh || !ctx->mesh.swap_pending()) return CUDAPT_OK;

@@ -1,5 +1,6 @@
 // Host driver of the mesh scene: BVH build + upload, wavefront state, per-pass launch sequence.
 #include "mesh_host.h"
+#include "lbvh_build.h"
 
 #include <algorithm>
 #include <chrono>
@@ -152,6 +153,90 @@ bool MeshScene::build_and_upload(std::string* err) {
   accel_bytes = nb + tb;
   if (!reupload(nullptr, err)) return false;
   MH_TRY(cudaDeviceSynchronize());
+  build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return true;
+}
+
+// Device build (lbvh_build.cu): the mesh goes up as it is (vertices, indices, material ids), the tree is built and
+// quantised on the GPU, and nodes | tris come BACK into the pinned staging and the host Bvh8 (for re-uploads, the host
+// refit path and the light list).  The device arrays the refit needs (vertices, indices, boxes) stay allocated.
+bool MeshScene::build_on_device(cudaStream_t stream, uint64_t* launches, std::string* err) {
+  const auto t0 = std::chrono::steady_clock::now();
+  if (!dev_) dev_ = new MeshDevice();
+  dev_->free_scene();
+  const uint32_t nt = (uint32_t)(indices_.size() / 3), nv = (uint32_t)(vertices_.size() / 3);
+  std::vector<cudapt_material> mats = materials_;
+  if (mats.empty()) {
+    cudapt_material d;
+    std::memset(&d, 0, sizeof(d));
+    d.albedo[0] = d.albedo[1] = d.albedo[2] = 0.7f;
+    mats.push_back(d);
+  }
+  Bvh8& bvh = dev_->bvh;
+  for (int k = 0; k < 3; ++k) bvh.world_lo[k] = INFINITY, bvh.world_hi[k] = -INFINITY;
+  for (size_t i = 0; i < (size_t)nv; ++i)
+    for (int k = 0; k < 3; ++k) {
+      bvh.world_lo[k] = std::min(bvh.world_lo[k], vertices_[3 * i + k]);
+      bvh.world_hi[k] = std::max(bvh.world_hi[k], vertices_[3 * i + k]);
+    }
+  const uint32_t node_cap = nt / 2u + 8u;
+  const size_t vb = sizeof(float) * 3 * (size_t)nv, ib = sizeof(uint32_t) * 3 * (size_t)nt;
+  uint32_t* d_mat_id = nullptr;
+  MH_TRY(cudaMalloc(&dev_->d_vertices, vb));
+  MH_TRY(cudaMalloc(&dev_->d_indices, ib));
+  MH_TRY(cudaMalloc(&dev_->d_tri_box, 24 * (size_t)nt));
+  MH_TRY(cudaMalloc(&dev_->d_node_box, 24 * (size_t)node_cap));
+  MH_TRY(cudaMallocHost(&dev_->h_pinned_vertices, vb));
+  MH_TRY(cudaMalloc(&dev_->d_nodes, sizeof(Bvh8Node) * (size_t)node_cap));
+  MH_TRY(cudaMalloc(&dev_->d_tris, sizeof(PackedTri) * (size_t)nt));
+  MH_TRY(cudaMalloc(&d_mat_id, sizeof(uint32_t) * (size_t)nt));
+  MH_TRY(cudaMemcpyAsync(dev_->d_vertices, vertices_.data(), vb, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_indices, indices_.data(), ib, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(d_mat_id, material_id_.data(), sizeof(uint32_t) * (size_t)nt, cudaMemcpyHostToDevice, stream));
+  LbvhResult r;
+  const bool built = build_lbvh_device(dev_->d_vertices, dev_->d_indices, d_mat_id, nt, bvh.world_lo, bvh.world_hi, dev_->d_nodes,
+                                       node_cap, dev_->d_tris, dev_->d_tri_box, dev_->d_node_box, &r, launches, stream, err);
+  cudaFree(d_mat_id);
+  if (!built) return false;
+  bvh.nodes.resize(r.n_nodes);
+  bvh.tris.resize(nt);
+  bvh.level_start = r.level_start;
+  bvh.max_depth = r.max_depth;
+  bvh.sah_cost = 0.0;
+  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
+  MH_TRY(cudaMallocHost(&dev_->h_pinned, nb + tb));
+  dev_->pinned_bytes = nb + tb;
+  MH_TRY(cudaMemcpyAsync(dev_->h_pinned, dev_->d_nodes, nb, cudaMemcpyDeviceToHost, stream));
+  MH_TRY(cudaMemcpyAsync((char*)dev_->h_pinned + nb, dev_->d_tris, tb, cudaMemcpyDeviceToHost, stream));
+  MH_TRY(cudaStreamSynchronize(stream));
+  std::memcpy(bvh.nodes.data(), dev_->h_pinned, nb);
+  std::memcpy(bvh.tris.data(), (char*)dev_->h_pinned + nb, tb);
+  bvh.tri_of_prim.assign(nt, 0u);
+  for (uint32_t k = 0; k < nt; ++k) {
+    if (bvh.tris[k].prim >= nt) {
+      *err = "internal error: device build produced an invalid triangle record";
+      return false;
+    }
+    bvh.tri_of_prim[bvh.tris[k].prim] = k;
+  }
+  dev_->lights.clear();
+  for (uint32_t i = 0; i < nt; ++i) {
+    uint32_t m = material_id_[i];
+    if (m >= mats.size()) m = 0;
+    if (mats[m].emission[0] > 0.f || mats[m].emission[1] > 0.f || mats[m].emission[2] > 0.f)
+      dev_->lights.push_back(bvh.tri_of_prim[i]);
+  }
+  dev_->materials = mats;
+  MH_TRY(cudaMalloc(&dev_->d_materials, mats.size() * sizeof(cudapt_material)));
+  MH_TRY(cudaMalloc(&dev_->d_lights, std::max<size_t>(dev_->lights.size(), 1) * sizeof(uint32_t)));
+  MH_TRY(cudaMemcpyAsync(dev_->d_materials, mats.data(), mats.size() * sizeof(cudapt_material), cudaMemcpyHostToDevice, stream));
+  if (!dev_->lights.empty())
+    MH_TRY(cudaMemcpyAsync(dev_->d_lights, dev_->lights.data(), dev_->lights.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                           stream));
+  MH_TRY(cudaStreamSynchronize(stream));
+  n_tris_built_ = nt;
+  n_nodes_built_ = r.n_nodes;
+  accel_bytes = nb + tb;
   build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return true;
 }

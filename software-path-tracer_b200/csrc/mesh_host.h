@@ -35,6 +35,7 @@ class MeshScene {
   void set_materials(const cudapt_material* m, uint32_t n);
   bool has_host_mesh() const { return !indices_.empty(); }
   bool build_and_upload(std::string* err);
+  bool build_on_device(cudaStream_t stream, uint64_t* launches, std::string* err);  // lbvh_build.cu
   // Same topology, moved vertices: refit the BVH on the host (no rebuild) and upload it again.
   // (on the device, refit.cu; CUDAPT_REFIT_HOST=1 selects the host implementation of the same code).
   bool update_vertices(const float* vertices, uint32_t nv, cudaStream_t stream, uint64_t* launches, std::string* err);
