@@ -22,7 +22,8 @@ for b in budgets:
     tr = pt.PathTracer(pt.default_config(**dict(wl["cfg"], samples_per_pass=spp)))
     tr.set_camera(pt.default_camera(tan_half_fov=wl["fov"]))
     tr.set_resolution(wl["w"], wl["h"])
-    tr.upload_mesh(scene["v"], scene["t"], scene["m"], scene["mats"])
+    tr.upload_mesh(scene["v"], scene["t"], scene["m"], scene["mats"], device_build=os.environ.get("PROBE_DEVICE_BUILD") == "1")
+    print(f"   accel build {tr.stats().accel_build_ms:.1f} ms, {tr.stats().n_nodes} nodes", flush=True)
     for counting in (False, True):
         tr.set_counting(counting)
         for _ in range(2):
