@@ -2,7 +2,7 @@
 // north star names next to the host SAH builder (bvh_build.cpp).  For scenes whose TOPOLOGY changes between frames:
 // a 1 M-triangle tree in milliseconds instead of ~0.6 s on 16 host threads, at the price of a worse tree (no SAH).
 //
-//   1. morton_kernel        63-bit Morton code of every triangle's box centre inside the scene bounds
+//   1. morton_kernel        63-bit Morton code of every triangle's box centre inside the scene's bounding cube
 //   2. cub::DeviceRadixSort (keys, triangle ids)                       [library call: the sort is not our hot path]
 //   3. radix_tree_kernel    binary radix tree over the sorted codes, one thread per internal node (Karras 2012:
 //                           "Maximizing Parallelism in the Construction of BVHs, Octrees, and k-d Trees"; ties between
@@ -297,7 +297,11 @@ bool build_lbvh_device(const float* d_vertices, const uint32_t* d_indices, const
     t.box = d_bin_box;
     const float ex = world_hi[0] - world_lo[0], ey = world_hi[1] - world_lo[1], ez = world_hi[2] - world_lo[2];
     const float3 lo = make_float3(world_lo[0], world_lo[1], world_lo[2]);
-    const float3 inv = make_float3(ex > 0.f ? 1.0f / ex : 0.f, ey > 0.f ? 1.0f / ey : 0.f, ez > 0.f ? 1.0f / ez : 0.f);
+    // ONE cell size for the three axes (the bounding cube, not the bounding box): with per-axis normalisation a flat
+    // scene (C4: 120 x 0.3 x 120) is cut along its thin axis at every third level, into halves that both span it
+    const float emax = fmaxf(ex, fmaxf(ey, ez));
+    const float ie = emax > 0.f ? 1.0f / emax : 0.f;
+    const float3 inv = make_float3(ie, ie, ie);
     morton_kernel<<<(n + 255u) / 256u, 256, 0, stream>>>(d_vertices, d_indices, n, lo, inv, d_keys, d_ids, d_prim_box);
     ++*launches;
     LB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, d_keys, d_keys2, d_ids, d_ids2, (int)n, 0, 63, stream));
