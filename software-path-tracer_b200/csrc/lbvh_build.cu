@@ -264,8 +264,8 @@ __global__ void __launch_bounds__(128) collapse_level_kernel(Bin2 t, const Box3*
 
 bool build_lbvh_device(const float* d_vertices, const uint32_t* d_indices, const uint32_t* d_material_id, uint32_t nt,
                        const float world_lo[3], const float world_hi[3], void* d_nodes, uint32_t node_capacity, void* d_tris,
-                       void* d_tri_box, void* d_node_box, LbvhResult* out, uint64_t* launches, cudaStream_t stream,
-                       std::string* err) {
+                       void* d_tri_box, void* d_node_box, LbvhResult* out, LbvhScratch* scratch, uint64_t* launches,
+                       cudaStream_t stream, std::string* err) {
   if (nt < 2) {
     *err = "the device builder needs at least two triangles";
     return false;
@@ -282,16 +282,33 @@ bool build_lbvh_device(const float* d_vertices, const uint32_t* d_indices, const
   std::vector<uint32_t> level_start;
   uint32_t n_level = 1, n_nodes = 1;
   {
-    LB_TRY(cudaMalloc(&d_keys, sizeof(uint64_t) * n));
-    LB_TRY(cudaMalloc(&d_keys2, sizeof(uint64_t) * n));
-    LB_TRY(cudaMalloc(&d_ids, sizeof(uint32_t) * n));
-    LB_TRY(cudaMalloc(&d_ids2, sizeof(uint32_t) * n));
-    LB_TRY(cudaMalloc(&d_prim_box, sizeof(Box3) * n));
-    LB_TRY(cudaMalloc(&d_bin_box, sizeof(Box3) * n));
-    LB_TRY(cudaMalloc(&d_u32, sizeof(uint32_t) * (size_t)n * 7));  // left, right, first, count, arrivals: n each; parent: 2n
-    LB_TRY(cudaMalloc(&d_counters, sizeof(uint32_t) * 4));
-    LB_TRY(cudaMalloc(&d_q0, sizeof(Work) * (size_t)node_capacity));
-    LB_TRY(cudaMalloc(&d_q1, sizeof(Work) * (size_t)node_capacity));
+    // one arena for all the temporaries, kept by the caller across rebuilds (a dozen cudaMalloc/cudaFree pairs cost
+    // more than the kernels at 1 M triangles)
+    LB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, d_keys, d_keys2, d_ids, d_ids2, (int)n, 0, 63, stream));
+    size_t off = 0;
+    auto take = [&off](size_t bytes) {
+      const size_t at = off;
+      off += (bytes + 255u) & ~(size_t)255u;
+      return at;
+    };
+    const size_t o_keys = take(sizeof(uint64_t) * n), o_keys2 = take(sizeof(uint64_t) * n), o_ids = take(sizeof(uint32_t) * n);
+    const size_t o_ids2 = take(sizeof(uint32_t) * n), o_prim = take(sizeof(Box3) * n), o_bin = take(sizeof(Box3) * n);
+    const size_t o_u32 = take(sizeof(uint32_t) * (size_t)n * 7);  // left, right, first, count, arrivals: n each; parent: 2n
+    const size_t o_cnt = take(sizeof(uint32_t) * 4), o_q0 = take(sizeof(Work) * (size_t)node_capacity);
+    const size_t o_q1 = take(sizeof(Work) * (size_t)node_capacity), o_sort = take(sort_bytes);
+    if (scratch->bytes < off) {
+      cudaFree(scratch->p);
+      scratch->p = nullptr, scratch->bytes = 0;
+      LB_TRY(cudaMalloc(&scratch->p, off));
+      scratch->bytes = off;
+    }
+    char* base = static_cast<char*>(scratch->p);
+    d_keys = reinterpret_cast<uint64_t*>(base + o_keys), d_keys2 = reinterpret_cast<uint64_t*>(base + o_keys2);
+    d_ids = reinterpret_cast<uint32_t*>(base + o_ids), d_ids2 = reinterpret_cast<uint32_t*>(base + o_ids2);
+    d_prim_box = reinterpret_cast<Box3*>(base + o_prim), d_bin_box = reinterpret_cast<Box3*>(base + o_bin);
+    d_u32 = reinterpret_cast<uint32_t*>(base + o_u32), d_counters = reinterpret_cast<uint32_t*>(base + o_cnt);
+    d_q0 = reinterpret_cast<Work*>(base + o_q0), d_q1 = reinterpret_cast<Work*>(base + o_q1);
+    d_sort_tmp = base + o_sort;
     t.left = d_u32, t.right = d_u32 + n, t.first = d_u32 + 2 * (size_t)n, t.count = d_u32 + 3 * (size_t)n;
     t.arrivals = d_u32 + 4 * (size_t)n, t.parent = d_u32 + 5 * (size_t)n;
     t.box = d_bin_box;
@@ -304,8 +321,6 @@ bool build_lbvh_device(const float* d_vertices, const uint32_t* d_indices, const
     const float3 inv = make_float3(ie, ie, ie);
     morton_kernel<<<(n + 255u) / 256u, 256, 0, stream>>>(d_vertices, d_indices, n, lo, inv, d_keys, d_ids, d_prim_box);
     ++*launches;
-    LB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, d_keys, d_keys2, d_ids, d_ids2, (int)n, 0, 63, stream));
-    LB_TRY(cudaMalloc(&d_sort_tmp, sort_bytes));
     LB_TRY(cub::DeviceRadixSort::SortPairs(d_sort_tmp, sort_bytes, d_keys, d_keys2, d_ids, d_ids2, (int)n, 0, 63, stream));
     LB_TRY(cudaMemsetAsync(t.arrivals, 0, sizeof(uint32_t) * n, stream));
     radix_tree_kernel<<<(n + 254u) / 256u, 256, 0, stream>>>(d_keys2, (int)n, t);
@@ -355,8 +370,6 @@ bool build_lbvh_device(const float* d_vertices, const uint32_t* d_indices, const
     out->max_depth = (uint32_t)level_start.size();
   }
 done:
-  cudaFree(d_keys), cudaFree(d_keys2), cudaFree(d_ids), cudaFree(d_ids2), cudaFree(d_prim_box), cudaFree(d_bin_box);
-  cudaFree(d_u32), cudaFree(d_counters), cudaFree(d_q0), cudaFree(d_q1), cudaFree(d_sort_tmp);
   return ok;
 }
 

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -39,6 +40,9 @@ struct MeshDevice {
   void* d_tri_box = nullptr;
   void* d_node_box = nullptr;
   void* h_pinned_vertices = nullptr;
+  uint32_t* d_material_id = nullptr;           // device build only
+  LbvhScratch lbvh_scratch;                    // device build only: the builder's temporaries, kept between builds
+  uint32_t device_cap_nt = 0, device_cap_nv = 0;  // sizes the device-build buffers were allocated for (0: host build)
   // wavefront state
   WavefrontState st{};
   uint32_t state_paths = 0;     // capacity in paths
@@ -64,8 +68,11 @@ struct MeshDevice {
       e = nullptr;
     }
     copy_stream = nullptr, ev_copy_done = nullptr, current = 0, swap_pending = false;
-    cudaFree(d_vertices), cudaFree(d_indices), cudaFree(d_tri_box), cudaFree(d_node_box);
-    d_vertices = nullptr, d_indices = nullptr, d_tri_box = nullptr, d_node_box = nullptr;
+    cudaFree(d_vertices), cudaFree(d_indices), cudaFree(d_tri_box), cudaFree(d_node_box), cudaFree(d_material_id);
+    d_vertices = nullptr, d_indices = nullptr, d_tri_box = nullptr, d_node_box = nullptr, d_material_id = nullptr;
+    device_cap_nt = device_cap_nv = 0;
+    cudaFree(lbvh_scratch.p);
+    lbvh_scratch = LbvhScratch{};
     if (h_pinned_vertices) cudaFreeHost(h_pinned_vertices);
     h_pinned_vertices = nullptr;
     staging_stale = false;
@@ -162,9 +169,38 @@ bool MeshScene::build_and_upload(std::string* err) {
 // refit path and the light list).  The device arrays the refit needs (vertices, indices, boxes) stay allocated.
 bool MeshScene::build_on_device(cudaStream_t stream, uint64_t* launches, std::string* err) {
   const auto t0 = std::chrono::steady_clock::now();
+  const bool dbg = std::getenv("CUDAPT_BUILD_DEBUG") != nullptr;
+  auto mark = [&](const char* what) {
+    if (dbg) std::fprintf(stderr, "[device build] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  };
   if (!dev_) dev_ = new MeshDevice();
-  dev_->free_scene();
   const uint32_t nt = (uint32_t)(indices_.size() / 3), nv = (uint32_t)(vertices_.size() / 3);
+  const uint32_t node_cap = nt / 2u + 8u;
+  const size_t vb = sizeof(float) * 3 * (size_t)nv, ib = sizeof(uint32_t) * 3 * (size_t)nt;
+  const size_t nb_cap = sizeof(Bvh8Node) * (size_t)node_cap, tb = sizeof(PackedTri) * (size_t)nt;
+  // A REbuild of a mesh of the same size (the per-frame case) keeps every allocation: pinned memory alone costs ~20 ms
+  // to allocate at 1 M triangles, three times the build itself.
+  const bool reuse = dev_->device_cap_nt == nt && dev_->device_cap_nv == nv && dev_->d_nodes && dev_->h_pinned;
+  if (!reuse) {
+    dev_->free_scene();
+    MH_TRY(cudaMalloc(&dev_->d_vertices, vb));
+    MH_TRY(cudaMalloc(&dev_->d_indices, ib));
+    MH_TRY(cudaMalloc(&dev_->d_tri_box, 24 * (size_t)nt));
+    MH_TRY(cudaMalloc(&dev_->d_node_box, 24 * (size_t)node_cap));
+    MH_TRY(cudaMallocHost(&dev_->h_pinned_vertices, vb));
+    MH_TRY(cudaMalloc(&dev_->d_nodes, nb_cap));
+    MH_TRY(cudaMalloc(&dev_->d_tris, tb));
+    MH_TRY(cudaMalloc(&dev_->d_material_id, sizeof(uint32_t) * (size_t)nt));
+    MH_TRY(cudaMallocHost(&dev_->h_pinned, nb_cap + tb));  // sized for the node capacity: the node count changes per build
+    dev_->pinned_bytes = nb_cap + tb;
+    dev_->device_cap_nt = nt;
+    dev_->device_cap_nv = nv;
+  } else {
+    MH_TRY(cudaStreamSynchronize(stream));
+    dev_->swap_pending = false;  // a staged copy of the previous tree is dropped (its buffer is capacity-sized, see stage)
+    cudaFree(dev_->d_materials), cudaFree(dev_->d_lights);
+    dev_->d_materials = nullptr, dev_->d_lights = nullptr;
+  }
   std::vector<cudapt_material> mats = materials_;
   if (mats.empty()) {
     cudapt_material d;
@@ -179,52 +215,44 @@ bool MeshScene::build_on_device(cudaStream_t stream, uint64_t* launches, std::st
       bvh.world_lo[k] = std::min(bvh.world_lo[k], vertices_[3 * i + k]);
       bvh.world_hi[k] = std::max(bvh.world_hi[k], vertices_[3 * i + k]);
     }
-  const uint32_t node_cap = nt / 2u + 8u;
-  const size_t vb = sizeof(float) * 3 * (size_t)nv, ib = sizeof(uint32_t) * 3 * (size_t)nt;
-  uint32_t* d_mat_id = nullptr;
-  MH_TRY(cudaMalloc(&dev_->d_vertices, vb));
-  MH_TRY(cudaMalloc(&dev_->d_indices, ib));
-  MH_TRY(cudaMalloc(&dev_->d_tri_box, 24 * (size_t)nt));
-  MH_TRY(cudaMalloc(&dev_->d_node_box, 24 * (size_t)node_cap));
-  MH_TRY(cudaMallocHost(&dev_->h_pinned_vertices, vb));
-  MH_TRY(cudaMalloc(&dev_->d_nodes, sizeof(Bvh8Node) * (size_t)node_cap));
-  MH_TRY(cudaMalloc(&dev_->d_tris, sizeof(PackedTri) * (size_t)nt));
-  MH_TRY(cudaMalloc(&d_mat_id, sizeof(uint32_t) * (size_t)nt));
-  MH_TRY(cudaMemcpyAsync(dev_->d_vertices, vertices_.data(), vb, cudaMemcpyHostToDevice, stream));
+  std::memcpy(dev_->h_pinned_vertices, vertices_.data(), vb);
+  MH_TRY(cudaMemcpyAsync(dev_->d_vertices, dev_->h_pinned_vertices, vb, cudaMemcpyHostToDevice, stream));
   MH_TRY(cudaMemcpyAsync(dev_->d_indices, indices_.data(), ib, cudaMemcpyHostToDevice, stream));
-  MH_TRY(cudaMemcpyAsync(d_mat_id, material_id_.data(), sizeof(uint32_t) * (size_t)nt, cudaMemcpyHostToDevice, stream));
+  MH_TRY(cudaMemcpyAsync(dev_->d_material_id, material_id_.data(), sizeof(uint32_t) * (size_t)nt, cudaMemcpyHostToDevice, stream));
+  mark("allocations + mesh upload");
   LbvhResult r;
-  const bool built = build_lbvh_device(dev_->d_vertices, dev_->d_indices, d_mat_id, nt, bvh.world_lo, bvh.world_hi, dev_->d_nodes,
-                                       node_cap, dev_->d_tris, dev_->d_tri_box, dev_->d_node_box, &r, launches, stream, err);
-  cudaFree(d_mat_id);
-  if (!built) return false;
+  if (!build_lbvh_device(dev_->d_vertices, dev_->d_indices, dev_->d_material_id, nt, bvh.world_lo, bvh.world_hi, dev_->d_nodes,
+                         node_cap, dev_->d_tris, dev_->d_tri_box, dev_->d_node_box, &r, &dev_->lbvh_scratch, launches, stream, err))
+    return false;
+  mark("tree built on the device");
   bvh.nodes.resize(r.n_nodes);
   bvh.tris.resize(nt);
   bvh.level_start = r.level_start;
   bvh.max_depth = r.max_depth;
   bvh.sah_cost = 0.0;
-  const size_t nb = bvh.nodes.size() * sizeof(Bvh8Node), tb = bvh.tris.size() * sizeof(PackedTri);
-  MH_TRY(cudaMallocHost(&dev_->h_pinned, nb + tb));
-  dev_->pinned_bytes = nb + tb;
-  MH_TRY(cudaMemcpyAsync(dev_->h_pinned, dev_->d_nodes, nb, cudaMemcpyDeviceToHost, stream));
-  MH_TRY(cudaMemcpyAsync((char*)dev_->h_pinned + nb, dev_->d_tris, tb, cudaMemcpyDeviceToHost, stream));
-  MH_TRY(cudaStreamSynchronize(stream));
-  std::memcpy(bvh.nodes.data(), dev_->h_pinned, nb);
-  std::memcpy(bvh.tris.data(), (char*)dev_->h_pinned + nb, tb);
-  bvh.tri_of_prim.assign(nt, 0u);
-  for (uint32_t k = 0; k < nt; ++k) {
-    if (bvh.tris[k].prim >= nt) {
-      *err = "internal error: device build produced an invalid triangle record";
-      return false;
-    }
-    bvh.tri_of_prim[bvh.tris[k].prim] = k;
-  }
+  // The tree lives on the device; the pinned staging and the host copy follow on demand (re-upload, staging, host
+  // refit: refresh_staging) -- except that a scene with emissive materials needs the leaf order of its lights now.
+  dev_->staging_stale = true;
   dev_->lights.clear();
-  for (uint32_t i = 0; i < nt; ++i) {
-    uint32_t m = material_id_[i];
-    if (m >= mats.size()) m = 0;
-    if (mats[m].emission[0] > 0.f || mats[m].emission[1] > 0.f || mats[m].emission[2] > 0.f)
-      dev_->lights.push_back(bvh.tri_of_prim[i]);
+  bool any_emissive = false;
+  for (const cudapt_material& m : mats) any_emissive = any_emissive || m.emission[0] > 0.f || m.emission[1] > 0.f || m.emission[2] > 0.f;
+  if (any_emissive) {
+    if (!refresh_staging(stream, err)) return false;
+    bvh.tri_of_prim.assign(nt, 0u);
+    for (uint32_t k = 0; k < nt; ++k) {
+      if (bvh.tris[k].prim >= nt) {
+        *err = "internal error: device build produced an invalid triangle record";
+        return false;
+      }
+      bvh.tri_of_prim[bvh.tris[k].prim] = k;
+    }
+    for (uint32_t i = 0; i < nt; ++i) {
+      uint32_t m = material_id_[i];
+      if (m >= mats.size()) m = 0;
+      if (mats[m].emission[0] > 0.f || mats[m].emission[1] > 0.f || mats[m].emission[2] > 0.f)
+        dev_->lights.push_back(bvh.tri_of_prim[i]);
+    }
+    mark("read-back + light list");
   }
   dev_->materials = mats;
   MH_TRY(cudaMalloc(&dev_->d_materials, mats.size() * sizeof(cudapt_material)));
@@ -236,8 +264,9 @@ bool MeshScene::build_on_device(cudaStream_t stream, uint64_t* launches, std::st
   MH_TRY(cudaStreamSynchronize(stream));
   n_tris_built_ = nt;
   n_nodes_built_ = r.n_nodes;
-  accel_bytes = nb + tb;
+  accel_bytes = bvh.nodes.size() * sizeof(Bvh8Node) + tb;
   build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  mark("done");
   return true;
 }
 
@@ -268,7 +297,10 @@ bool MeshScene::stage(cudaStream_t render_stream, std::string* err) {
   if (dev_->staging_stale && !refresh_staging(render_stream, err)) return false;
   const size_t nb = dev_->bvh.nodes.size() * sizeof(Bvh8Node), tb = dev_->bvh.tris.size() * sizeof(PackedTri);
   if (!dev_->d_nodes_shadow) {
-    MH_TRY(cudaMalloc(&dev_->d_nodes_shadow, nb));
+    // after a device build the two node buffers trade places with every swap, and a rebuild writes up to the node
+    // CAPACITY into whichever is current
+    const size_t nb_alloc = dev_->device_cap_nt ? sizeof(Bvh8Node) * (size_t)(dev_->device_cap_nt / 2u + 8u) : nb;
+    MH_TRY(cudaMalloc(&dev_->d_nodes_shadow, nb_alloc));
     MH_TRY(cudaMalloc(&dev_->d_tris_shadow, tb));
     MH_TRY(cudaStreamCreateWithFlags(&dev_->copy_stream, cudaStreamNonBlocking));
     MH_TRY(cudaEventCreateWithFlags(&dev_->ev_copy_done, cudaEventDisableTiming));

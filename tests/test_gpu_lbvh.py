@@ -111,3 +111,43 @@ def test_device_build_of_one_million_triangles(pt, scenes):
           f"host SAH build {sh.accel_build_ms:.0f} ms ({sh.n_nodes} nodes)")
     assert ms < sh.accel_build_ms
     trd.close(), trh.close()
+
+
+@pytest.mark.parametrize("name", ["heightfield", "cornell"])
+def test_rebuild_in_place_reuses_buffers_and_matches_a_fresh_build(pt, scenes, name):
+    """A second device build of a mesh of the SAME size keeps every allocation (mesh_host.cu build_on_device); the
+    pinned staging and the host copy of the tree are fetched lazily.  Moved vertices + rebuild must equal a fresh
+    tracer's build bit for bit, including through staging, re-upload and with emissive triangles (light list)."""
+    kw = dict(max_bounces=4, jitter=1, seed=5)
+    cam = None
+    if name == "heightfield":
+        scene = scenes.heightfield(n_quads=64)
+    else:
+        scene = scenes.cornell_box(sphere_res=8)
+        kw.update(nee=1, sky_scale=0.0)
+        cam = dict(tan_half_fov=0.36)
+    v0, idx, mid, mats = scene
+    rng = np.random.default_rng(2)
+    v1 = (v0 + rng.uniform(-0.02, 0.02, v0.shape)).astype(np.float32)
+    W, H, N = 96, 54, 4
+    _, want, want_prim, _ = render(pt, (v1, idx, mid, mats), W, H, N, True, cam, **kw)
+
+    tr, _, _, _ = render(pt, scene, W, H, N, True, cam, **kw)
+    for step in range(3):
+        tr.upload_mesh(v1 if step != 1 else v0, idx, mid, mats, device_build=True)
+        if step == 2:
+            tr.stage_scene()                                   # shadow copy of the rebuilt tree, swapped at render
+        tr.reset()
+        tr.render(N)
+        if step != 1:
+            acc, _ = tr.read_accum()
+            prim, _ = tr.read_primary_hits()
+            assert np.array_equal(prim, want_prim)
+            assert np.array_equal(bits(acc), bits(want))
+    # after the swap the current node buffer is the former shadow: rebuild into it, then re-upload from staging
+    tr.upload_mesh(v1, idx, mid, mats, device_build=True)
+    tr.reupload_scene()
+    tr.reset()
+    tr.render(N)
+    acc, _ = tr.read_accum()
+    assert np.array_equal(bits(acc), bits(want))
