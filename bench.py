@@ -499,6 +499,21 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
         t = json.load(open(tpath)).get(wl["name"])
         if t:
             traffic = t["dram_bytes_per_ray"] * closest_rays / n_launches
+    # what the memory system gives a per-thread 16-B gather (tools/microbench_l2.cu run on this pool's B200): the
+    # ceiling the algorithmic bytes of an L2-resident BVH can be fetched at, beside the HBM copy peak above
+    gather = None
+    lpath = os.path.join(ROOT, "profiles", "l2_bandwidth.json")
+    if os.path.exists(lpath):
+        rows = json.load(open(lpath))["rows"]
+        def row(mib, pat):
+            return next((r["GBps"] for r in rows if r["set_MiB"] == mib and r["pattern"] == pat), None)
+        big = wl["name"] == "c4"
+        gather = {"l2_stream_GBps": row(64, "stream"),
+                  "record_gather_GBps": row(1100 if big else 64, "node80_per_thread"),
+                  "working_set": "1.1 GiB (HBM)" if big else "64 MiB (L2-resident)",
+                  "frac_of_record_gather": (achieved / row(1100 if big else 64, "node80_per_thread")) if achieved else None,
+                  "source": "profiles/l2_bandwidth.json (tools/microbench_l2.cu): every thread fetches whole 80-B records at "
+                            "hashed addresses with 16-B loads; rays of one warp share nodes, so the kernel can exceed it"}
     packets = None
     if st.packet_rays:
         packets = {"kernel": "primary_packet_kernel", "share_of_step": st.last_packet_ms / render_ms if render_ms else None,
@@ -515,6 +530,7 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
             "peak_source": peak_src, "bytes_per_ray": 44.0 + Nn * 80.0 + Nt * 48.0, "bytes_per_path_whole_step": bytes_per_path,
             "whole_step_GBps": bytes_per_path * n_px * spp / (render_ms * 1e-3) / 1e9,
             "R": R, "Nn": Nn, "Nt": Nt, "B": B, "rays_traced_by_this_kernel_per_step": closest_rays, "packets": packets,
+            "gather_ceiling": gather,
             "note": "Nn/Nt: nodes / triangles per ray of the per-ray kernel (camera rays finished by packets excluded). "
                     "BVH of c2/c3 is L2-resident, so DRAM traffic is far below the algorithmic bytes and the kernel is "
                     "issue bound (profiles/r01_notes.md); c4 (1.3 GB BVH) is the HBM-gather case"}
