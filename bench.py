@@ -357,6 +357,7 @@ def main():
 
     # ---- e2e through the C ABI with host buffers: scene H2D + render + resolve + RGBA8 D2H every step ----
     host_rgba = np.empty((H, W), np.uint32)
+    tr.host_register(host_rgba)   # the caller's result buffer, page-locked as the C++ adapter does (host/CUDAPathTracer.cpp)
 
     def e2e_step(first=True, last=True):
         # The step's scene goes host -> device inside the timed region.  Mesh scenes are double-buffered: the copy for
@@ -374,7 +375,7 @@ def main():
             tr.set_frame_count(spp * world if rank == 0 else spp)
         if fused:
             if rank == 0:
-                host_rgba[...] = tr.download_rgba8()   # the image the ranks assembled in the root's buffer: D2H + sync
+                tr.download_rgba8(host_rgba)   # the image the ranks assembled in the root's buffer: D2H + sync
             else:
                 tr.synchronize()
         else:
@@ -447,6 +448,7 @@ def main():
         line["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Msamples/s", "cores": cores, "kind": kind,
                                 "sample": desc, "mrays_per_s": rays / sec / 1e6}
     print(json.dumps(line), flush=True)
+    tr.host_unregister(host_rgba)
     tr.close()
     if world > 1:
         dist.destroy_process_group()

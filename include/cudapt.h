@@ -193,6 +193,13 @@ int cudapt_synchronize(cudapt_ctx* ctx);
 /* ---- read-back: get_render_result(), CPT.cpp:87-117 + Color.h:7-10 --------------------------------- */
 /* accum/frame_count -> clamp[0,1] -> (uint8)(c*255) -> R<<24|G<<16|B<<8|A, W*H words, row 0 on top. */
 int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out);
+/* Page-lock a caller-owned host buffer (RenderResult::image_buffer, PathTracer.h:23-29) so that
+ * cudapt_resolve_rgba8 / cudapt_download_rgba8 / cudapt_read_accum copy straight into it; an ordinary buffer goes
+ * through the library's pinned staging + one memcpy (8 MB at 1080p: ~1 ms per read-back).  Thin wrappers over
+ * cudaHostRegister / cudaHostUnregister, here so that the C++ host does not have to link the CUDA runtime.
+ * Unregister before the buffer is freed or resized. */
+int cudapt_host_register(cudapt_ctx* ctx, void* host_ptr, size_t bytes);
+int cudapt_host_unregister(cudapt_ctx* ctx, void* host_ptr);
 /* Post-process stage applied by cudapt_resolve_rgba8 between the division by frame_count and the 8-bit pack
  * (SURVEY.md 8f-2).  Reference anchors: the exposure multiply commented out at CPT.cpp:101-104 with
  * RenderSettings::getExposure()/getAutoExposure()/getTargetLuminance() (Types.h:57-58,67-69), and the

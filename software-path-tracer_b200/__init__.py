@@ -74,7 +74,7 @@ EXPORTS = [
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
     "cudapt_build_accel_device", "cudapt_reupload_scene", "cudapt_stage_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
-    "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_read_accum",
+    "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_host_register", "cudapt_host_unregister", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
     "cudapt_set_frame_count",
@@ -125,6 +125,8 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_render.argtypes = [vp, u32]
     lib.cudapt_synchronize.argtypes = [vp]
     lib.cudapt_resolve_rgba8.argtypes = [vp, vp]
+    lib.cudapt_host_register.argtypes = [vp, vp, ctypes.c_size_t]
+    lib.cudapt_host_unregister.argtypes = [vp, vp]
     lib.cudapt_read_accum.argtypes = [vp, vp, ctypes.POINTER(u32)]
     lib.cudapt_write_accum.argtypes = [vp, vp, u32]
     lib.cudapt_read_primary_hits.argtypes = [vp, vp, vp]
@@ -312,6 +314,13 @@ class PathTracer:
         self._chk(self._lib.cudapt_resolve_rgba8(self._h, _p(out)))
         return out
 
+    def host_register(self, a: np.ndarray):
+        """Page-lock a caller-owned array: read-backs into it skip the staging copy (cudapt_host_register)."""
+        self._chk(self._lib.cudapt_host_register(self._h, _p(a), ctypes.c_size_t(a.nbytes)))
+
+    def host_unregister(self, a: np.ndarray):
+        self._chk(self._lib.cudapt_host_unregister(self._h, _p(a)))
+
     def set_postprocess(self, post: PostProcess):
         self._chk(self._lib.cudapt_set_postprocess(self._h, ctypes.byref(post)))
 
@@ -365,8 +374,9 @@ class PathTracer:
                                                         ctypes.c_void_p(int(root_rgba)),
                                                         ctypes.c_void_p(int(root_accum)) if root_accum else None))
 
-    def download_rgba8(self) -> np.ndarray:
-        out = np.empty((self.height, self.width), np.uint32)
+    def download_rgba8(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width), np.uint32)
         self._chk(self._lib.cudapt_download_rgba8(self._h, _p(out)))
         return out
 

@@ -562,8 +562,20 @@ int cudapt_get_exposure(cudapt_ctx* ctx, float* exposure) {
 }
 
 namespace {
-// resolve (+ auto-exposure) into d_rgba and the pinned staging buffer; synchronises the stream
-int resolve_to_pinned(cudapt_ctx* ctx, const char* who) {
+// true when the D2H copy can land in the caller's buffer directly: page-locked host memory (cudaMallocHost, or
+// registered with cudapt_host_register / cudaHostRegister)
+bool host_is_pinned(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// resolve (+ auto-exposure) into d_rgba and `dst` (page-locked: the library's staging buffer when null);
+// synchronises the stream
+int resolve_to_pinned(cudapt_ctx* ctx, const char* who, uint32_t* dst = nullptr) {
   if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "%s: resolution not set", who);
   if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "%s: no frames rendered yet", who);
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
@@ -592,7 +604,7 @@ int resolve_to_pinned(cudapt_ctx* ctx, const char* who) {
                                     ctx->stream));
     ctx->launches += 1;
   }
-  CU_TRY(ctx, cudaMemcpyAsync(ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(ctx, cudaMemcpyAsync(dst ? dst : ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   ctx->last_exposure = pp.exposure;
   if (d_exposure) CU_TRY(ctx, cudaMemcpyAsync(&ctx->last_exposure, d_exposure, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -602,9 +614,32 @@ int resolve_to_pinned(cudapt_ctx* ctx, const char* who) {
 
 int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
   if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  // page-locked destination: the copy engine writes the image where the caller wants it (no staging copy)
+  if (host_is_pinned(host_out)) return resolve_to_pinned(ctx, "cudapt_resolve_rgba8", host_out);
   const int rc = resolve_to_pinned(ctx, "cudapt_resolve_rgba8");
   if (rc != CUDAPT_OK) return rc;
   std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * (size_t)ctx->width * ctx->height);
+  return CUDAPT_OK;
+}
+
+int cudapt_host_register(cudapt_ctx* ctx, void* host_ptr, size_t bytes) {
+  if (!ctx || !host_ptr || bytes == 0) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const cudaError_t e = cudaHostRegister(host_ptr, bytes, cudaHostRegisterDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError();  // not sticky: the context stays usable
+    return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_host_register: %s", cudaGetErrorString(e));
+  }
+  return CUDAPT_OK;
+}
+int cudapt_host_unregister(cudapt_ctx* ctx, void* host_ptr) {
+  if (!ctx || !host_ptr) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const cudaError_t e = cudaHostUnregister(host_ptr);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_host_unregister: %s", cudaGetErrorString(e));
+  }
   return CUDAPT_OK;
 }
 
@@ -860,9 +895,10 @@ int cudapt_download_rgba8(cudapt_ctx* ctx, uint32_t* host_out) {
   if (!ctx->d_rgba) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_download_rgba8: resolution not set");
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   const size_t n = (size_t)ctx->width * ctx->height;
-  CU_TRY(ctx, cudaMemcpyAsync(ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, ctx->stream));
+  const bool direct = host_is_pinned(host_out);
+  CU_TRY(ctx, cudaMemcpyAsync(direct ? host_out : ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, ctx->stream));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * n);
+  if (!direct) std::memcpy(host_out, ctx->h_pinned_rgba, sizeof(uint32_t) * n);
   return finish_timing(ctx);
 }
 

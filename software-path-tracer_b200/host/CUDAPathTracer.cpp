@@ -35,6 +35,8 @@ namespace render
 
 	CUDAPathTracer::~CUDAPathTracer()
 	{
+		if (m_result_pinned)
+			cudapt_host_unregister(m_ctx, m_render_result.image_buffer.data());
 		cudapt_destroy(m_ctx);
 	}
 
@@ -73,7 +75,12 @@ namespace render
 		{
 			m_render_result.width = m_renderSettings->getWidth();
 			m_render_result.height = m_renderSettings->getHeight();
+			// the result buffer is page-locked, so that get_render_result()'s device-to-host copy lands in it directly
+			if (m_result_pinned)
+				cudapt_host_unregister(m_ctx, m_render_result.image_buffer.data());
 			m_render_result.image_buffer.resize((size_t)m_render_result.width * m_render_result.height);
+			m_result_pinned = !m_render_result.image_buffer.empty() &&
+				cudapt_host_register(m_ctx, m_render_result.image_buffer.data(), m_render_result.image_buffer.size() * sizeof(uint32_t)) == CUDAPT_OK;
 			check_status(m_ctx, cudapt_set_resolution(m_ctx, m_render_result.width, m_render_result.height), "cudapt_set_resolution");
 			m_frameCount = 0;
 			restart = false;  // set_resolution zeroes the accumulation buffer

@@ -49,6 +49,7 @@ namespace render
 		std::shared_ptr<RenderSettings> m_renderSettings;
 		PathTracer::RenderResult m_render_result;
 		uint32_t m_frameCount = 0;
+		bool m_result_pinned = false;  // m_render_result.image_buffer is registered with cudapt_host_register
 	};
 
 	// What the factory case added in INTEGRATION.md calls.

@@ -118,3 +118,26 @@ def test_invalid_postprocess_rejected(pt, rendered):
         tr.set_postprocess(pt.default_postprocess(tonemap=7))
     with pytest.raises(pt.CudaptError):
         tr.set_postprocess(pt.default_postprocess(exposure=-1.0))
+
+
+def test_pinned_result_buffer(pt, scenes):
+    """cudapt_host_register: a page-locked caller buffer receives the read-back directly (no staging copy); the
+    bytes equal those of an ordinary buffer, and an unregistered pointer cannot be unregistered."""
+    with pt.PathTracer() as tr:
+        tr.set_resolution(96, 54)
+        tr.upload_spheres(scenes.app_spheres())
+        tr.render(3)
+        plain = tr.resolve_rgba8()
+        pinned = np.full((54, 96), 0xDEADBEEF, np.uint32)
+        tr.host_register(pinned)
+        try:
+            out = tr.resolve_rgba8(pinned)
+            assert out is pinned and np.array_equal(pinned, plain)
+            pinned[...] = 0
+            tr.download_rgba8(pinned)
+            assert np.array_equal(pinned, plain)
+        finally:
+            tr.host_unregister(pinned)
+        with pytest.raises(pt.CudaptError):
+            tr.host_unregister(plain)
+        assert np.array_equal(tr.resolve_rgba8(), plain)   # the context still works after the failed call
