@@ -180,7 +180,8 @@ def run_reference_arm(args, wl, scene, rank, world):
         "impl": "reference", "metric": "Msamples/s (paths/s)", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["desc"], "name": wl["name"]},
+        "config": {"workload": wl["desc"], "name": wl["name"], "width": wl["w"], "height": wl["h"], "spp_per_gpu": wl["spp"],
+                   "partition": "host CPU only (rank 0)"},
         "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc,
                          "mrays_per_s": rays / sec / 1e6},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
