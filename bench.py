@@ -357,10 +357,16 @@ def main():
     rays_per_path = st.rays / max(st.paths, 1)
 
     # ---- e2e through the C ABI with host buffers: scene H2D + render + resolve + RGBA8 D2H every step ----
-    host_rgba = np.empty((H, W), np.uint32)
-    tr.host_register(host_rgba)   # the caller's result buffer, page-locked as the C++ adapter does (host/CUDAPathTracer.cpp)
+    # The caller's result buffers: page-locked (as the C++ adapter pins RenderResult::image_buffer) and TWO of them,
+    # because the read-back is double-buffered -- cudapt_resolve_rgba8_async / cudapt_download_rgba8_async copy image
+    # k to the host on the library's download stream while step k+1 renders, as a viewer that shows frame k while
+    # frame k+1 renders would.  Every step's image still crosses to the host inside the timed region; the host waits
+    # for copy k-1 before it starts copy k, so it never runs more than one step ahead of the GPU.
+    host_rgba = [np.empty((H, W), np.uint32) for _ in range(2)]
+    for b in host_rgba:
+        tr.host_register(b)
 
-    def e2e_step(first=True, last=True):
+    def e2e_step(k=0, first=True, last=True):
         # The step's scene goes host -> device inside the timed region.  Mesh scenes are double-buffered: the copy for
         # step k+1 (cudapt_stage_scene, the library's copy stream) is started as soon as step k's kernels are queued and
         # overlaps them; step k+1's render waits for it and swaps the buffers.  The first step uploads in line.
@@ -371,24 +377,28 @@ def main():
         tr.render(frames_per_render)
         if wl["kind"] == "mesh" and not last:
             tr.stage_scene()                         # next step's scene: H2D concurrent with this step's rendering
+        if fused and rank == 0:
+            tr.stream_wait_download()                # the peers rewrite the root's image after the rendezvous in tail()
         tail()
         if world > 1:
             tr.set_frame_count(spp * world if rank == 0 else spp)
         if fused:
             if rank == 0:
-                tr.download_rgba8(host_rgba)   # the image the ranks assembled in the root's buffer: D2H + sync
-            else:
-                tr.synchronize()
+                tr.wait_download()                             # image k-1 is on the host
+                tr.download_rgba8_async(host_rgba[k & 1])      # the image the ranks assembled in the root's buffer
         else:
-            tr.resolve_rgba8(host_rgba)              # resolve kernel + D2H + sync
+            tr.wait_download()
+            tr.resolve_rgba8_async(host_rgba[k & 1])          # resolve kernel + D2H, not waited for here
 
     e2e_step()
+    tr.wait_download()
     sync_all()
     t0 = time.perf_counter()
     e2e_marks = []
     for k in range(args.steps):
-        e2e_step(first=(k == 0), last=(k == args.steps - 1))   # exactly one scene upload per step
+        e2e_step(k, first=(k == 0), last=(k == args.steps - 1))   # exactly one scene upload per step
         e2e_marks.append(time.perf_counter())
+    tr.wait_download()                                            # the last image is on the host
     sync_all()
     if os.environ.get("BENCH_DEBUG"):
         print(f"[rank {rank}] e2e step s {[round(b - a, 4) for a, b in zip([t0] + e2e_marks[:-1], e2e_marks)]}", file=sys.stderr, flush=True)
@@ -449,7 +459,8 @@ def main():
         line["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Msamples/s", "cores": cores, "kind": kind,
                                 "sample": desc, "mrays_per_s": rays / sec / 1e6}
     print(json.dumps(line), flush=True)
-    tr.host_unregister(host_rgba)
+    for b in host_rgba:
+        tr.host_unregister(b)
     tr.close()
     if world > 1:
         dist.destroy_process_group()

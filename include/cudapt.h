@@ -200,6 +200,19 @@ int cudapt_resolve_rgba8(cudapt_ctx* ctx, uint32_t* host_out);
  * Unregister before the buffer is freed or resized. */
 int cudapt_host_register(cudapt_ctx* ctx, void* host_ptr, size_t bytes);
 int cudapt_host_unregister(cudapt_ctx* ctx, void* host_ptr);
+/* Double-buffered read-back for a viewer that shows frame k while frame k+1 renders (App.cpp:231-238 calls render()
+ * and get_render_result() back to back every UI frame).  cudapt_resolve_rgba8_async enqueues the resolve on the
+ * context's stream and the device-to-host copy on a second stream and returns at once; host_out must be page-locked
+ * (CUDAPT_ERR_INVALID otherwise) and holds the image once cudapt_wait_download returns.  Rendering calls made in
+ * between overlap the copy; the next call that rewrites the 8-bit image waits for it on the device.  One read-back
+ * can be in flight: wait before starting the next one into the same buffer.  Not with auto-exposure (its result is
+ * read back synchronously).  cudapt_download_rgba8_async is the same for an image already in the context's 8-bit
+ * buffer (cudapt_reduce_resolve_peers on the root); there the ROOT calls cudapt_stream_wait_download before the
+ * rendezvous that lets the peers write the next image, which makes its stream wait for the pending copy. */
+int cudapt_resolve_rgba8_async(cudapt_ctx* ctx, uint32_t* host_out);
+int cudapt_download_rgba8_async(cudapt_ctx* ctx, uint32_t* host_out);
+int cudapt_wait_download(cudapt_ctx* ctx);
+int cudapt_stream_wait_download(cudapt_ctx* ctx);
 /* Post-process stage applied by cudapt_resolve_rgba8 between the division by frame_count and the 8-bit pack
  * (SURVEY.md 8f-2).  Reference anchors: the exposure multiply commented out at CPT.cpp:101-104 with
  * RenderSettings::getExposure()/getAutoExposure()/getTargetLuminance() (Types.h:57-58,67-69), and the

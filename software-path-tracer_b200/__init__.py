@@ -74,7 +74,8 @@ EXPORTS = [
     "cudapt_abi_version", "cudapt_set_resolution", "cudapt_set_config", "cudapt_set_camera",
     "cudapt_upload_spheres", "cudapt_upload_mesh", "cudapt_upload_materials", "cudapt_build_accel",
     "cudapt_build_accel_device", "cudapt_reupload_scene", "cudapt_stage_scene", "cudapt_update_vertices", "cudapt_debug_accel_checksum",
-    "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_host_register", "cudapt_host_unregister", "cudapt_read_accum",
+    "cudapt_reset", "cudapt_render", "cudapt_synchronize", "cudapt_resolve_rgba8", "cudapt_host_register", "cudapt_host_unregister",
+    "cudapt_resolve_rgba8_async", "cudapt_download_rgba8_async", "cudapt_wait_download", "cudapt_stream_wait_download", "cudapt_read_accum",
     "cudapt_write_accum", "cudapt_read_primary_hits", "cudapt_get_stats", "cudapt_set_counting",
     "cudapt_set_tile_partition", "cudapt_set_frame_range", "cudapt_accum_device_ptr", "cudapt_stream",
     "cudapt_set_frame_count",
@@ -127,6 +128,10 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_resolve_rgba8.argtypes = [vp, vp]
     lib.cudapt_host_register.argtypes = [vp, vp, ctypes.c_size_t]
     lib.cudapt_host_unregister.argtypes = [vp, vp]
+    lib.cudapt_resolve_rgba8_async.argtypes = [vp, vp]
+    lib.cudapt_download_rgba8_async.argtypes = [vp, vp]
+    lib.cudapt_wait_download.argtypes = [vp]
+    lib.cudapt_stream_wait_download.argtypes = [vp]
     lib.cudapt_read_accum.argtypes = [vp, vp, ctypes.POINTER(u32)]
     lib.cudapt_write_accum.argtypes = [vp, vp, u32]
     lib.cudapt_read_primary_hits.argtypes = [vp, vp, vp]
@@ -317,6 +322,19 @@ class PathTracer:
     def host_register(self, a: np.ndarray):
         """Page-lock a caller-owned array: read-backs into it skip the staging copy (cudapt_host_register)."""
         self._chk(self._lib.cudapt_host_register(self._h, _p(a), ctypes.c_size_t(a.nbytes)))
+
+    def resolve_rgba8_async(self, out: np.ndarray):
+        """Resolve + D2H into the page-locked `out` without waiting (cudapt_resolve_rgba8_async); wait_download() next."""
+        self._chk(self._lib.cudapt_resolve_rgba8_async(self._h, _p(out)))
+
+    def download_rgba8_async(self, out: np.ndarray):
+        self._chk(self._lib.cudapt_download_rgba8_async(self._h, _p(out)))
+
+    def wait_download(self):
+        self._chk(self._lib.cudapt_wait_download(self._h))
+
+    def stream_wait_download(self):
+        self._chk(self._lib.cudapt_stream_wait_download(self._h))
 
     def host_unregister(self, a: np.ndarray):
         self._chk(self._lib.cudapt_host_unregister(self._h, _p(a)))

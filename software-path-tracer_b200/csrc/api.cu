@@ -22,7 +22,12 @@ struct cudapt_ctx {
   cudapt_config cfg{};
   cudapt_camera cam{};
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // CUDA-event pairs around the cudapt_render() calls whose time has not been collected yet: a small ring, so that
+  // renders can be queued back to back without the host waiting for the previous one (cudapt_render never blocks
+  // unless kTimingRing renders are in flight)
+  static constexpr int kTimingRing = 4;
+  cudaEvent_t ev0[kTimingRing] = {}, ev1[kTimingRing] = {};
+  int timing_head = 0, timing_count = 0;  // oldest uncollected pair, number of uncollected pairs
   std::string err;
   int sm_count = 0;
 
@@ -34,6 +39,11 @@ struct cudapt_ctx {
   unsigned long long* d_counters = nullptr;
   uint32_t* h_pinned_rgba = nullptr;  // pinned staging for the 8-bit read-back
   size_t pinned_pixels = 0;
+  // asynchronous read-back (cudapt_resolve_rgba8_async / cudapt_download_rgba8_async): the copy runs on its own
+  // stream, after ev_img_ready (image complete on `stream`), and signals ev_dl_done
+  cudaStream_t dl_stream = nullptr;
+  cudaEvent_t ev_img_ready = nullptr, ev_dl_done = nullptr;
+  bool dl_pending = false;
 
   // scene
   enum SceneKind { kNone, kSpheres, kMesh } scene = kNone;
@@ -61,7 +71,6 @@ struct cudapt_ctx {
   // stats
   uint64_t launches = 0;
   double render_ms = 0.0, last_render_ms = 0.0, last_trace_ms = 0.0, last_packet_ms = 0.0;
-  bool timing_pending = false;
 };
 
 namespace {
@@ -143,17 +152,39 @@ int restart_accumulation(cudapt_ctx* ctx) {  // CPT.cpp:151-154
   return CUDAPT_OK;
 }
 
-int finish_timing(cudapt_ctx* ctx) {
-  if (!ctx->timing_pending) return CUDAPT_OK;
-  CU_TRY(ctx, cudaEventSynchronize(ctx->ev1));
-  float ms = 0.f;
-  CU_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-  ctx->last_render_ms = ms;
-  ctx->last_trace_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_trace_ms() : 0.0;
-  ctx->last_packet_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_packet_ms() : 0.0;
-  ctx->render_ms += ms;
-  ctx->timing_pending = false;
+// Collects the time of finished renders: waits for the `wait_for` oldest ones, then takes those that have completed.
+int collect_timing(cudapt_ctx* ctx, int wait_for) {
+  bool any = false;
+  while (ctx->timing_count > 0) {
+    const int k = ctx->timing_head;
+    if (wait_for > 0) {
+      CU_TRY(ctx, cudaEventSynchronize(ctx->ev1[k]));
+      --wait_for;
+    } else if (cudaEventQuery(ctx->ev1[k]) != cudaSuccess) {
+      cudaGetLastError();  // cudaErrorNotReady is not an error here
+      break;
+    }
+    float ms = 0.f;
+    CU_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev0[k], ctx->ev1[k]));
+    ctx->last_render_ms = ms;
+    ctx->render_ms += ms;
+    ctx->timing_head = (k + 1) % cudapt_ctx::kTimingRing;
+    --ctx->timing_count;
+    any = true;
+  }
+  // per-kernel event pairs of the mesh integrator belong to the most recent render: read them only when nothing is in flight
+  if (any && ctx->timing_count == 0) {
+    ctx->last_trace_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_trace_ms() : 0.0;
+    ctx->last_packet_ms = ctx->scene == cudapt_ctx::kMesh ? ctx->mesh.collect_packet_ms() : 0.0;
+  }
   return CUDAPT_OK;
+}
+int finish_timing(cudapt_ctx* ctx) { return collect_timing(ctx, ctx->timing_count); }
+
+bool create_timing_events(cudapt_ctx* ctx) {
+  for (int k = 0; k < cudapt_ctx::kTimingRing; ++k)
+    if (cudaEventCreate(&ctx->ev0[k]) != cudaSuccess || cudaEventCreate(&ctx->ev1[k]) != cudaSuccess) return false;
+  return true;
 }
 
 void free_spheres(cudapt_ctx* ctx) {
@@ -260,7 +291,7 @@ int cudapt_create(const cudapt_config* cfg, cudapt_ctx** out) {
   cudapt_default_postprocess(&ctx->post);
   ctx->mesh.sm_count = ctx->sm_count;
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+      !create_timing_events(ctx) ||
       cudaMalloc(&ctx->d_counters, sizeof(unsigned long long) * kCntSlots) != cudaSuccess ||
       cudaMemset(ctx->d_counters, 0, sizeof(unsigned long long) * kCntSlots) != cudaSuccess) {
     fail(nullptr, CUDAPT_ERR_CUDA, "cudapt_create: stream/event/counter setup failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -285,8 +316,16 @@ void cudapt_destroy(cudapt_ctx* ctx) {
   cudaFree(ctx->d_lum_partials);
   cudaFree(ctx->d_env);
   if (ctx->h_pinned_rgba) cudaFreeHost(ctx->h_pinned_rgba);
-  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
-  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->dl_stream) {
+    cudaStreamSynchronize(ctx->dl_stream);
+    cudaStreamDestroy(ctx->dl_stream);
+  }
+  if (ctx->ev_img_ready) cudaEventDestroy(ctx->ev_img_ready);
+  if (ctx->ev_dl_done) cudaEventDestroy(ctx->ev_dl_done);
+  for (int k = 0; k < cudapt_ctx::kTimingRing; ++k) {
+    if (ctx->ev0[k]) cudaEventDestroy(ctx->ev0[k]);
+    if (ctx->ev1[k]) cudaEventDestroy(ctx->ev1[k]);
+  }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -298,6 +337,10 @@ int cudapt_set_resolution(cudapt_ctx* ctx, uint32_t width, uint32_t height) {
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
   if (width != ctx->width || height != ctx->height || !ctx->d_accum) {  // CPT.cpp:140-149
     CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->dl_pending) {  // an asynchronous read-back still reads the old image buffer
+      CU_TRY(ctx, cudaEventSynchronize(ctx->ev_dl_done));
+      ctx->dl_pending = false;
+    }
     cudaFree(ctx->d_accum);
     cudaFree(ctx->d_rgba);
     cudaFree(ctx->d_aov_prim);
@@ -479,12 +522,14 @@ int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
   if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_render: resolution not set");
   if (n_frames == 0) return CUDAPT_OK;
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
-  int rc = finish_timing(ctx);
+  // the time of finished renders is collected without waiting; only a full ring makes the host wait for the oldest
+  int rc = collect_timing(ctx, ctx->timing_count == cudapt_ctx::kTimingRing ? 1 : 0);
   if (rc) return rc;
   if ((rc = commit_staged_scene(ctx)) != CUDAPT_OK) return rc;
+  const int tk = (ctx->timing_head + ctx->timing_count) % cudapt_ctx::kTimingRing;
   const uint32_t first = ctx->frame_first + ctx->frame_count * ctx->frame_stride;  // 1-based (CPT.cpp:61)
   const bool want_aov = ctx->frame_count == 0;
-  CU_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  CU_TRY(ctx, cudaEventRecord(ctx->ev0[tk], ctx->stream));
   if (ctx->scene == cudapt_ctx::kSpheres) {
     SphereLaunch a;
     a.spheres = ctx->d_spheres;
@@ -524,8 +569,8 @@ int cudapt_render(cudapt_ctx* ctx, uint32_t n_frames) {
     if (e != cudaSuccess) return fail(ctx, CUDAPT_ERR_CUDA, "cudapt_render(mesh): %s: %s", err.c_str(), cudaGetErrorString(e));
     ctx->launches += launched;
   }
-  CU_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  ctx->timing_pending = true;
+  CU_TRY(ctx, cudaEventRecord(ctx->ev1[tk], ctx->stream));
+  ++ctx->timing_count;
   ctx->frame_count += n_frames;
   return CUDAPT_OK;
 }
@@ -573,12 +618,20 @@ bool host_is_pinned(const void* p) {
   return at.type == cudaMemoryTypeHost;
 }
 
-// resolve (+ auto-exposure) into d_rgba and `dst` (page-locked: the library's staging buffer when null);
-// synchronises the stream
-int resolve_to_pinned(cudapt_ctx* ctx, const char* who, uint32_t* dst = nullptr) {
+// A pending asynchronous read-back still reads d_rgba: whatever writes the image next waits for it (device side).
+int order_after_download(cudapt_ctx* ctx) {
+  if (ctx->dl_pending) CU_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_dl_done, 0));
+  return CUDAPT_OK;
+}
+
+// resolve (+ auto-exposure) kernels into d_rgba, enqueued on the stream; *d_exposure_out = the device exposure value
+// when auto-exposure is on
+int enqueue_resolve(cudapt_ctx* ctx, const char* who, const float** d_exposure_out) {
   if (!ctx->d_accum) return fail(ctx, CUDAPT_ERR_INVALID, "%s: resolution not set", who);
   if (ctx->frame_count == 0) return fail(ctx, CUDAPT_ERR_NO_FRAMES, "%s: no frames rendered yet", who);
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  const int rc = order_after_download(ctx);
+  if (rc != CUDAPT_OK) return rc;
   const uint32_t n = ctx->width * ctx->height;
   const cudapt_postprocess& pp = ctx->post;
   const bool plain = pp.exposure == 1.0f && pp.tonemap == CUDAPT_TONEMAP_NONE && !pp.srgb && !pp.auto_exposure;
@@ -604,11 +657,40 @@ int resolve_to_pinned(cudapt_ctx* ctx, const char* who, uint32_t* dst = nullptr)
                                     ctx->stream));
     ctx->launches += 1;
   }
+  *d_exposure_out = d_exposure;
+  return CUDAPT_OK;
+}
+
+// resolve (+ auto-exposure) into d_rgba and `dst` (page-locked: the library's staging buffer when null);
+// synchronises the stream
+int resolve_to_pinned(cudapt_ctx* ctx, const char* who, uint32_t* dst = nullptr) {
+  const float* d_exposure = nullptr;
+  const int rc = enqueue_resolve(ctx, who, &d_exposure);
+  if (rc != CUDAPT_OK) return rc;
+  const uint32_t n = ctx->width * ctx->height;
   CU_TRY(ctx, cudaMemcpyAsync(dst ? dst : ctx->h_pinned_rgba, ctx->d_rgba, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
-  ctx->last_exposure = pp.exposure;
+  ctx->last_exposure = ctx->post.exposure;
   if (d_exposure) CU_TRY(ctx, cudaMemcpyAsync(&ctx->last_exposure, d_exposure, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
   CU_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return finish_timing(ctx);
+}
+
+// D2H of d_rgba into the caller's page-locked buffer on the download stream, after everything queued on `stream`
+int enqueue_download(cudapt_ctx* ctx, const char* who, uint32_t* host_out) {
+  if (!host_is_pinned(host_out))
+    return fail(ctx, CUDAPT_ERR_INVALID, "%s: the destination must be page-locked (cudapt_host_register)", who);
+  if (!ctx->dl_stream) {
+    CU_TRY(ctx, cudaStreamCreateWithFlags(&ctx->dl_stream, cudaStreamNonBlocking));
+    CU_TRY(ctx, cudaEventCreateWithFlags(&ctx->ev_img_ready, cudaEventDisableTiming));
+    CU_TRY(ctx, cudaEventCreateWithFlags(&ctx->ev_dl_done, cudaEventDisableTiming));
+  }
+  CU_TRY(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->stream));
+  CU_TRY(ctx, cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_img_ready, 0));
+  CU_TRY(ctx, cudaMemcpyAsync(host_out, ctx->d_rgba, sizeof(uint32_t) * (size_t)ctx->width * ctx->height, cudaMemcpyDeviceToHost,
+                              ctx->dl_stream));
+  CU_TRY(ctx, cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
+  ctx->dl_pending = true;
+  return CUDAPT_OK;
 }
 }  // namespace
 
@@ -632,6 +714,40 @@ int cudapt_host_register(cudapt_ctx* ctx, void* host_ptr, size_t bytes) {
   }
   return CUDAPT_OK;
 }
+int cudapt_resolve_rgba8_async(cudapt_ctx* ctx, uint32_t* host_out) {
+  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  if (ctx->post.auto_exposure) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_resolve_rgba8_async: auto-exposure reads its result back; use cudapt_resolve_rgba8");
+  if (!host_is_pinned(host_out))
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_resolve_rgba8_async: the destination must be page-locked (cudapt_host_register)");
+  const float* d_exposure = nullptr;
+  const int rc = enqueue_resolve(ctx, "cudapt_resolve_rgba8_async", &d_exposure);
+  if (rc != CUDAPT_OK) return rc;
+  ctx->last_exposure = ctx->post.exposure;
+  return enqueue_download(ctx, "cudapt_resolve_rgba8_async", host_out);
+}
+
+int cudapt_download_rgba8_async(cudapt_ctx* ctx, uint32_t* host_out) {
+  if (!ctx || !host_out) return CUDAPT_ERR_INVALID;
+  if (!ctx->d_rgba) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_download_rgba8_async: resolution not set");
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  return enqueue_download(ctx, "cudapt_download_rgba8_async", host_out);
+}
+
+int cudapt_wait_download(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  if (!ctx->dl_pending) return CUDAPT_OK;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  CU_TRY(ctx, cudaEventSynchronize(ctx->ev_dl_done));
+  ctx->dl_pending = false;
+  return finish_timing(ctx);
+}
+
+int cudapt_stream_wait_download(cudapt_ctx* ctx) {
+  if (!ctx) return CUDAPT_ERR_INVALID;
+  CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+  return order_after_download(ctx);
+}
+
 int cudapt_host_unregister(cudapt_ctx* ctx, void* host_ptr) {
   if (!ctx || !host_ptr) return CUDAPT_ERR_INVALID;
   CU_TRY(ctx, cudaSetDevice(ctx->cfg.device));

@@ -141,3 +141,72 @@ def test_pinned_result_buffer(pt, scenes):
         with pytest.raises(pt.CudaptError):
             tr.host_unregister(plain)
         assert np.array_equal(tr.resolve_rgba8(), plain)   # the context still works after the failed call
+
+
+def test_async_readback_double_buffered(pt, scenes):
+    """cudapt_resolve_rgba8_async / cudapt_wait_download: the image lands in a page-locked buffer while later renders
+    are already queued; bytes equal the synchronous read-back of the same frame count; ordinary memory is refused."""
+    with pt.PathTracer() as tr:
+        tr.set_resolution(160, 90)
+        tr.upload_spheres(scenes.app_spheres())
+        bufs = [np.zeros((90, 160), np.uint32) for _ in range(2)]
+        for b in bufs:
+            tr.host_register(b)
+        try:
+            want = []
+            for k in range(4):      # reference: synchronous read-back after 1, 2, 3, 4 frames
+                tr.render(1)
+                want.append(tr.resolve_rgba8().copy())
+            tr.reset()
+            got = []
+            for k in range(4):      # the same, double-buffered: image k is collected after render k+1 was queued
+                tr.render(1)
+                tr.wait_download()
+                if k:
+                    got.append(bufs[(k - 1) & 1].copy())
+                tr.resolve_rgba8_async(bufs[k & 1])
+            tr.render(3)            # queued behind the pending copy; must not disturb it
+            tr.wait_download()
+            got.append(bufs[3 & 1].copy())
+            for k in range(4):
+                assert np.array_equal(got[k], want[k]), k
+            assert tr.stats().frame_count == 7
+            tr.wait_download()      # nothing pending: returns at once
+            with pytest.raises(pt.CudaptError):
+                tr.resolve_rgba8_async(np.zeros((90, 160), np.uint32))
+            # a synchronous read-back right behind an asynchronous one waits for it on the device
+            tr.resolve_rgba8_async(bufs[0])
+            sync = tr.resolve_rgba8()
+            tr.wait_download()
+            assert np.array_equal(sync, bufs[0])
+            # resizing with a copy in flight waits for it
+            tr.resolve_rgba8_async(bufs[1])
+            tr.set_resolution(64, 36)
+            assert np.array_equal(bufs[1], sync)
+        finally:
+            tr.wait_download()
+            for b in bufs:
+                tr.host_unregister(b)
+
+
+def test_renders_queue_without_blocking_and_stats_add_up(pt, scenes):
+    """cudapt_render no longer waits for the previous render's timing events: many renders can be queued back to back
+    (more than the ring of event pairs), and render_ms still covers every one of them."""
+    v, t, m, mats = scenes.heightfield(n_quads=48)
+    with pt.PathTracer(pt.default_config(rng_mode=1, samples_per_pass=32, max_bounces=3, jitter=1, seed=1)) as tr:
+        tr.set_resolution(128, 72)
+        tr.upload_mesh(v, t, m, mats)
+        tr.render(32)
+        a1, _ = tr.read_accum()
+        tr.reset()
+        for _ in range(9):
+            tr.render(32)
+        tr.synchronize()
+        st = tr.stats()
+        # every one of the nine renders is in render_ms (each takes about as long as the last)
+        assert st.frame_count == 9 * 32 and st.last_render_ms > 0.0 and st.last_trace_ms > 0.0
+        assert st.render_ms > 9 * 0.6 * st.last_render_ms
+        tr.reset()
+        tr.render(32)
+        a2, _ = tr.read_accum()
+        assert np.array_equal(a1.view(np.uint32), a2.view(np.uint32))
