@@ -234,8 +234,9 @@ int cudapt_set_postprocess(cudapt_ctx* ctx, const cudapt_postprocess* pp);
 int cudapt_get_exposure(cudapt_ctx* ctx, float* exposure);
 /* Image writer for headless use (the reference only displays through SDL, App.cpp:236-238):
  * ".png" = 8-bit RGBA and ".ppm" = binary P6 of the post-processed image, ".pfm" = float RGB accum/frame_count
- * (bottom row first, little endian), chosen by the file extension.  The PNG is written without a compression
- * library (stored deflate blocks). */
+ * (bottom row first, little endian), ".exr" = the same linear floats as an OpenEXR 2 scan-line file (32-bit FLOAT
+ * channels B G R, uncompressed), chosen by the file extension.  PNG and EXR are written without a codec library
+ * (stored deflate blocks / uncompressed scan lines). */
 int cudapt_write_image(cudapt_ctx* ctx, const char* path);
 
 /* Float accumulation (private m_accumulation_buffer, CPT.h:72): 4*W*H floats RGBA, and the frame count. */

@@ -825,13 +825,81 @@ std::vector<unsigned char> encode_png_rgba8(const uint32_t* packed, uint32_t W, 
 }
 }  // namespace
 
+namespace {
+// OpenEXR 2, single-part scan-line image, 32-bit FLOAT channels B G R (the file format orders channels by name),
+// no compression, one scan line per block, increasing y: linear radiance accum / frames, nothing else.
+void put_le(std::vector<unsigned char>& v, const void* p, size_t n) {  // the box is little-endian, as the format
+  const unsigned char* b = static_cast<const unsigned char*>(p);
+  v.insert(v.end(), b, b + n);
+}
+void put_i32(std::vector<unsigned char>& v, int32_t x) { put_le(v, &x, 4); }
+void put_f32(std::vector<unsigned char>& v, float x) { put_le(v, &x, 4); }
+void put_str(std::vector<unsigned char>& v, const char* s) { put_le(v, s, std::strlen(s) + 1); }
+void put_attr(std::vector<unsigned char>& v, const char* name, const char* type, const std::vector<unsigned char>& value) {
+  put_str(v, name);
+  put_str(v, type);
+  put_i32(v, (int32_t)value.size());
+  v.insert(v.end(), value.begin(), value.end());
+}
+std::vector<unsigned char> encode_exr_rgb32f(const float* accum_rgba, uint32_t frames, uint32_t W, uint32_t H) {
+  std::vector<unsigned char> out;
+  const unsigned char magic[4] = {0x76, 0x2f, 0x31, 0x01};
+  put_le(out, magic, 4);
+  put_i32(out, 2);  // version 2, no flags: single-part scan lines, short names
+  std::vector<unsigned char> a;
+  for (const char* ch : {"B", "G", "R"}) {
+    put_str(a, ch);
+    put_i32(a, 2);  // FLOAT
+    const unsigned char lin_reserved[4] = {0, 0, 0, 0};
+    put_le(a, lin_reserved, 4);
+    put_i32(a, 1), put_i32(a, 1);  // x / y sampling
+  }
+  a.push_back(0);
+  put_attr(out, "channels", "chlist", a);
+  put_attr(out, "compression", "compression", {0});
+  a.clear();
+  put_i32(a, 0), put_i32(a, 0), put_i32(a, (int32_t)W - 1), put_i32(a, (int32_t)H - 1);
+  put_attr(out, "dataWindow", "box2i", a);
+  put_attr(out, "displayWindow", "box2i", a);
+  put_attr(out, "lineOrder", "lineOrder", {0});
+  a.clear();
+  put_f32(a, 1.0f);
+  put_attr(out, "pixelAspectRatio", "float", a);
+  a.clear();
+  put_f32(a, 0.0f), put_f32(a, 0.0f);
+  put_attr(out, "screenWindowCenter", "v2f", a);
+  a.clear();
+  put_f32(a, 1.0f);
+  put_attr(out, "screenWindowWidth", "float", a);
+  out.push_back(0);  // end of header
+  const size_t line_bytes = 3 * sizeof(float) * (size_t)W, block_bytes = 8 + line_bytes;
+  const uint64_t first = out.size() + 8 * (uint64_t)H;
+  for (uint32_t y = 0; y < H; ++y) {
+    const uint64_t off = first + block_bytes * (uint64_t)y;
+    put_le(out, &off, 8);
+  }
+  out.reserve(out.size() + block_bytes * (size_t)H);
+  std::vector<float> line(3 * (size_t)W);
+  for (uint32_t y = 0; y < H; ++y) {
+    put_i32(out, (int32_t)y);
+    put_i32(out, (int32_t)line_bytes);
+    for (int c = 0; c < 3; ++c)  // B, G, R planes of the line
+      for (uint32_t x = 0; x < W; ++x) line[(size_t)c * W + x] = accum_rgba[4 * ((size_t)y * W + x) + (2 - c)] / (float)frames;
+    put_le(out, line.data(), line_bytes);
+  }
+  return out;
+}
+}  // namespace
+
 int cudapt_write_image(cudapt_ctx* ctx, const char* path) {
   if (!ctx || !path) return CUDAPT_ERR_INVALID;
   const size_t len = std::strlen(path);
   const bool ppm = len > 4 && std::strcmp(path + len - 4, ".ppm") == 0;
   const bool pfm = len > 4 && std::strcmp(path + len - 4, ".pfm") == 0;
   const bool png = len > 4 && std::strcmp(path + len - 4, ".png") == 0;
-  if (!ppm && !pfm && !png) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: '%s' is neither .png, .ppm nor .pfm", path);
+  const bool exr = len > 4 && std::strcmp(path + len - 4, ".exr") == 0;
+  if (!ppm && !pfm && !png && !exr)
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: '%s' is neither .png, .ppm, .pfm nor .exr", path);
   const uint32_t W = ctx->width, H = ctx->height;
   if (png) {
     const int rc = resolve_to_pinned(ctx, "cudapt_write_image");
@@ -866,6 +934,14 @@ int cudapt_write_image(cudapt_ctx* ctx, const char* path) {
   uint32_t fc = 0;
   const int rc = cudapt_read_accum(ctx, acc.data(), &fc);
   if (rc != CUDAPT_OK) return rc;
+  if (exr) {
+    const std::vector<unsigned char> bytes = encode_exr_rgb32f(acc.data(), fc, W, H);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: cannot open '%s'", path);
+    const bool ok = std::fwrite(bytes.data(), 1, bytes.size(), f) == bytes.size();
+    std::fclose(f);
+    return ok ? CUDAPT_OK : fail(ctx, CUDAPT_ERR_INVALID, "cudapt_write_image: short write to '%s'", path);
+  }
   std::vector<float> rgb((size_t)W * H * 3);
   for (uint32_t y = 0; y < H; ++y)  // PFM stores the bottom row first
     for (uint32_t x = 0; x < W; ++x)

@@ -107,8 +107,49 @@ def test_image_writer(pt, oracle, rendered, tmp_path):
     assert not lines[:, 0].any()
     rgba = lines[:, 1:].reshape(H, W, 4)
     assert np.array_equal(rgba[..., :3].astype(np.int32), want) and np.all(rgba[..., 3] == 255)
+    # EXR: parsed with struct alone (OpenEXR 2 single-part scan-line layout), and by OpenCV when its codec is there
+    exr = str(tmp_path / "out.exr")
+    tr.write_image(exr)
+    raw = open(exr, "rb").read()
+    assert raw[:4] == bytes([0x76, 0x2F, 0x31, 0x01]) and struct.unpack("<i", raw[4:8]) == (2,)
+    pos, attrs = 8, {}
+    while raw[pos] != 0:
+        e = raw.index(b"\0", pos)
+        name = raw[pos:e].decode()
+        e2 = raw.index(b"\0", e + 1)
+        typ = raw[e + 1:e2].decode()
+        (size,) = struct.unpack("<i", raw[e2 + 1:e2 + 5])
+        attrs[name] = (typ, raw[e2 + 5:e2 + 5 + size])
+        pos = e2 + 5 + size
+    pos += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    assert struct.unpack("<4i", attrs["dataWindow"][1]) == (0, 0, W - 1, H - 1) and attrs["displayWindow"] == attrs["dataWindow"]
+    ch, names = attrs["channels"][1], []
+    q = 0
+    while ch[q] != 0:
+        e = ch.index(b"\0", q)
+        names.append(ch[q:e].decode())
+        assert struct.unpack("<i4xii", ch[e + 1:e + 17]) == (2, 1, 1)   # FLOAT, sampling 1 x 1
+        q = e + 17
+    assert names == ["B", "G", "R"]
+    offsets = struct.unpack(f"<{H}Q", raw[pos:pos + 8 * H])
+    assert offsets[0] == pos + 8 * H and len(raw) == offsets[-1] + 8 + 12 * W
+    img = np.empty((H, W, 3), np.float32)
+    for y, off in enumerate(offsets):
+        assert struct.unpack("<ii", raw[off:off + 8]) == (y, 12 * W)
+        planes = np.frombuffer(raw[off + 8:off + 8 + 12 * W], "<f4").reshape(3, W)
+        img[y] = planes[::-1].T                                        # B G R planes -> RGB
+    assert np.array_equal(img.view(np.uint32), (acc[..., :3] / np.float32(N)).view(np.uint32))
+    try:
+        os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+        import cv2
+        bgr = cv2.imread(exr, cv2.IMREAD_UNCHANGED)
+    except Exception:
+        bgr = None
+    if bgr is not None:
+        assert bgr.dtype == np.float32 and np.array_equal(bgr[..., ::-1].view(np.uint32), img.view(np.uint32))
     with pytest.raises(pt.CudaptError):
-        tr.write_image(str(tmp_path / "out.exr"))
+        tr.write_image(str(tmp_path / "out.tiff"))
     tr.set_postprocess(pt.default_postprocess())
 
 

@@ -4,7 +4,7 @@
  *
  *   cudapt_cli [--scene app | --obj FILE] [--size WxH] [--spp N] [--bounces N] [--philox] [--jitter]
  *              [--exposure X] [--auto-exposure] [--tonemap none|reinhard|aces] [--srgb] [--device D]
- *              [--look-at px,py,pz,tx,ty,tz,vfov] [--lens RADIUS] --out FILE.png|.ppm|.pfm
+ *              [--look-at px,py,pz,tx,ty,tz,vfov] [--lens RADIUS] --out FILE.png|.ppm|.pfm|.exr
  *
  * --scene app : the 38 spheres of App.cpp:101-122 with the reference integrator (default).
  * --obj FILE  : triangles of a Wavefront OBJ ("v" and "f" records; polygons are fanned), one grey Lambert material,
@@ -121,7 +121,7 @@ int main(int argc, char** argv) {
     }
   }
   if (!out || !w || !h || !spp) {
-    fprintf(stderr, "usage: cudapt_cli [--scene app | --obj FILE] [--size WxH] [--spp N] ... --out FILE.png|.ppm|.pfm\n");
+    fprintf(stderr, "usage: cudapt_cli [--scene app | --obj FILE] [--size WxH] [--spp N] ... --out FILE.png|.ppm|.pfm|.exr\n");
     return 2;
   }
   if (obj) {
