@@ -8,7 +8,7 @@ NVFLAGS  := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
             -Xcompiler -fPIC,-O2,-ffp-contract=off -Xptxas -v
 CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace_bvh.cu $(CSRC)/wavefront.cu $(CSRC)/post.cu $(CSRC)/refit.cu $(CSRC)/primary_packet.cu $(CSRC)/lbvh_build.cu
 HDR      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cudapt.h
-OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o
+OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o $(CSRC)/env_load.o
 
 all: $(PKG)/libcudapt.so oracle host build/cudapt_cli
 
@@ -17,6 +17,9 @@ $(CSRC)/%.o: $(CSRC)/%.cu $(HDR)
 
 $(CSRC)/bvh_build.o: $(CSRC)/bvh_build.cpp $(CSRC)/bvh8.h $(CSRC)/bvh8_refit.h
 	$(CXX) -std=c++17 -O2 -fPIC -ffp-contract=off -pthread -c -o $@ $<
+
+$(CSRC)/env_load.o: $(CSRC)/env_load.cpp $(CSRC)/env_load.h
+	$(CXX) -std=c++17 -O2 -fPIC -ffp-contract=off -c -o $@ $<
 
 $(PKG)/libcudapt.so: $(OBJ)
 	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $(OBJ) -lpthread

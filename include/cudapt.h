@@ -181,6 +181,17 @@ int cudapt_debug_accel_checksum(cudapt_ctx* ctx, uint64_t* nodes_sum, uint64_t* 
  * matches bit for bit.)  Both integrators use it; sky_scale still multiplies it.  rgb = NULL or size = 0 restores
  * the reference's procedural sky (CPT.cpp:286-292).  Restarts accumulation. */
 int cudapt_upload_environment(cudapt_ctx* ctx, const float* rgb, uint32_t size);
+/* The file form of the above -- what the commented-out Scene::setEnvironmentMap(filepath) did through OpenImageIO
+ * (Scene.cpp:124-169).  path is a LATITUDE-LONGITUDE panorama, ".pfm" (portable float map) or ".hdr" / ".pic"
+ * (Radiance RGBE, flat or run-length encoded), read without an image library; it is resampled once on the host
+ * (double precision, bilinear) into a size x size octahedral map and uploaded.  Panorama convention: column
+ * u = 1/2 + atan2(d.x, d.z) / 2pi (the image centre is +Z, the default camera's view direction), row v = acos(d.y) / pi
+ * (top row = +Y).  octahedral_out (size*size*3 floats) receives the texels that were uploaded, or NULL.
+ * CUDAPT_ERR_INVALID for an unreadable / unsupported file.  Restarts accumulation. */
+int cudapt_load_environment(cudapt_ctx* ctx, const char* path, uint32_t size, float* octahedral_out);
+/* Only the host half of the above (file -> octahedral texels); needs no device and no context, error text through
+ * cudapt_last_error(NULL). */
+int cudapt_convert_environment(const char* path, uint32_t size, float* octahedral_out);
 
 /* ---- progressive rendering: render(), CPT.cpp:43-85 ------------------------------------------------ */
 /* Zero the accumulation buffer, frame count = 0 (CPT.cpp:151-154). */

@@ -81,7 +81,7 @@ EXPORTS = [
     "cudapt_set_frame_count",
     "cudapt_reduce_resolve_peers", "cudapt_rgba_device_ptr", "cudapt_download_rgba8", "cudapt_ipc_export",
     "cudapt_ipc_open", "cudapt_ipc_close",
-    "cudapt_upload_environment", "cudapt_default_postprocess", "cudapt_set_postprocess", "cudapt_get_exposure", "cudapt_write_image",
+    "cudapt_upload_environment", "cudapt_load_environment", "cudapt_convert_environment", "cudapt_default_postprocess", "cudapt_set_postprocess", "cudapt_get_exposure", "cudapt_write_image",
 ]
 
 _lib = None
@@ -145,6 +145,8 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_stream.restype = vp
     lib.cudapt_set_frame_count.argtypes = [vp, u32]
     lib.cudapt_upload_environment.argtypes = [vp, vp, u32]
+    lib.cudapt_load_environment.argtypes = [vp, ctypes.c_char_p, u32, vp]
+    lib.cudapt_convert_environment.argtypes = [ctypes.c_char_p, u32, vp]
     lib.cudapt_reduce_resolve_peers.argtypes = [vp, ctypes.POINTER(vp), u32, u32, u32, vp, vp]
     lib.cudapt_rgba_device_ptr.argtypes = [vp]
     lib.cudapt_rgba_device_ptr.restype = vp
@@ -200,6 +202,16 @@ def default_postprocess(**kw) -> PostProcess:
             raise AttributeError(k)
         setattr(p, k, v)
     return p
+
+
+def convert_environment(path: str, size: int = 256) -> np.ndarray:
+    """Host only (no GPU): lat-long .pfm / .hdr panorama -> octahedral texels (size, size, 3)."""
+    lib = load_library()
+    out = np.empty((size, size, 3), np.float32)
+    rc = lib.cudapt_convert_environment(os.fsencode(path), size, out.ctypes.data)
+    if rc != 0:
+        raise CudaptError(rc, (lib.cudapt_last_error(None) or b"").decode())
+    return out
 
 
 def _p(a):
@@ -303,6 +315,12 @@ class PathTracer:
         self._chk(self._lib.cudapt_upload_environment(self._h, _p(e), e.shape[0]))
 
     # rendering
+    def load_environment(self, path: str, size: int = 256) -> np.ndarray:
+        """Lat-long .pfm / .hdr panorama -> octahedral map of `size`, uploaded; returns the texels (size, size, 3)."""
+        out = np.empty((size, size, 3), np.float32)
+        self._chk(self._lib.cudapt_load_environment(self._h, os.fsencode(path), size, _p(out)))
+        return out
+
     def reset(self):
         self._chk(self._lib.cudapt_reset(self._h))
 

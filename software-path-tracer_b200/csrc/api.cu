@@ -13,6 +13,7 @@
 #include <string>
 #include <vector>
 
+#include "env_load.h"
 #include "kernels.h"
 #include "mesh_host.h"
 
@@ -503,6 +504,26 @@ int cudapt_upload_environment(cudapt_ctx* ctx, const float* rgb, uint32_t size) 
     ctx->env_size = size;
   }
   return restart_accumulation(ctx);
+}
+
+int cudapt_convert_environment(const char* path, uint32_t size, float* octahedral_out) {  // host only, no device
+  if (!path || !octahedral_out) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_convert_environment: null argument");
+  if (size < 2u || size > 16384u) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_convert_environment: size %u", size);
+  LatLongImage im;
+  std::string err;
+  if (!load_latlong_image(path, &im, &err)) return fail(nullptr, CUDAPT_ERR_INVALID, "cudapt_convert_environment: %s", err.c_str());
+  latlong_to_octahedral(im, size, octahedral_out);
+  return CUDAPT_OK;
+}
+
+int cudapt_load_environment(cudapt_ctx* ctx, const char* path, uint32_t size, float* octahedral_out) {
+  if (!ctx || !path) return CUDAPT_ERR_INVALID;
+  if (size < 2u || size > 16384u) return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_load_environment: size %u", size);
+  std::vector<float> octa((size_t)size * size * 3);
+  if (cudapt_convert_environment(path, size, octa.data()) != CUDAPT_OK)
+    return fail(ctx, CUDAPT_ERR_INVALID, "cudapt_load_environment: %s", g_create_error.c_str());
+  if (octahedral_out) std::memcpy(octahedral_out, octa.data(), sizeof(float) * octa.size());
+  return cudapt_upload_environment(ctx, octa.data(), size);
 }
 
 int cudapt_reset(cudapt_ctx* ctx) {

@@ -4,6 +4,8 @@ The lookup uses only + - * / and comparisons, so the bar is the same as for the 
 path bit-identical on >= 99.99 % of pixels, mesh path on >= 99.9 %.  A miss-only pixel is a closed-form check:
 after N frames its value is N times the bilinear texel blend, summed in float.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -77,3 +79,42 @@ def test_environment_edge_cases(pt, oracle, scenes):
         assert np.all(bits(acc) == bits(np.broadcast_to(want, acc.shape)))
         with pytest.raises(pt.CudaptError):
             tr._chk(tr._lib.cudapt_upload_environment(tr._h, env.ctypes.data, 100000))
+
+
+def test_environment_from_file_matches_twin_and_cli(pt, oracle, scenes, tmp_path):
+    """cudapt_load_environment: a lat-long .pfm panorama, resampled on the host, renders exactly like the same texels
+    uploaded directly -- and like the CPU twin given those texels; cudapt_cli --env writes the same image."""
+    import subprocess
+    W, H, N = 96, 54, 4
+    yy, xx = np.mgrid[0:32, 0:64].astype(np.float32)
+    pano = np.stack([0.3 + xx / 64, 1.2 - yy / 32, 0.5 + 0.0 * xx], axis=-1).astype(np.float32)
+    pano[6:9, 40:44] = 40.0                                               # a small sun
+    path = str(tmp_path / "sky.pfm")
+    with open(path, "wb") as f:
+        f.write(b"PF\n64 32\n-1.0\n" + np.ascontiguousarray(pano[::-1], "<f4").tobytes())
+    sph = scenes.app_spheres()
+    with pt.PathTracer() as tr:
+        tr.set_resolution(W, H)
+        tr.upload_spheres(sph)
+        octa = tr.load_environment(path, 64)
+        assert np.array_equal(octa, pt.convert_environment(path, 64))
+        tr.render(N)
+        a_file, _ = tr.read_accum()
+        tr.upload_environment(octa)
+        tr.render(N)
+        a_direct, _ = tr.read_accum()
+        with pytest.raises(pt.CudaptError):
+            tr.load_environment(str(tmp_path / "missing.hdr"), 64)
+        tr.render(1)                                                      # the context survives the failed load
+    assert np.array_equal(a_file.view(np.uint32), a_direct.view(np.uint32))
+    want, _, _, _ = oracle.twin_render_spheres(oracle.twin_params(W, H, env=octa), sph, N)
+    assert same_frac(a_file, want) >= 0.9999
+    cli = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "build", "cudapt_cli")
+    if os.path.exists(cli):
+        out = str(tmp_path / "cli.pfm")
+        subprocess.run([cli, "--size", f"{W}x{H}", "--spp", str(N), "--env", path, "--env-size", "64", "--out", out], check=True,
+                       capture_output=True)
+        raw = open(out, "rb").read()
+        head = f"PF\n{W} {H}\n-1.0\n".encode()
+        img = np.frombuffer(raw[len(head):], "<f4").reshape(H, W, 3)[::-1]
+        assert np.array_equal(img.view(np.uint32), (a_file[..., :3] / np.float32(N)).view(np.uint32))

@@ -4,11 +4,13 @@
  *
  *   cudapt_cli [--scene app | --obj FILE] [--size WxH] [--spp N] [--bounces N] [--philox] [--jitter]
  *              [--exposure X] [--auto-exposure] [--tonemap none|reinhard|aces] [--srgb] [--device D]
- *              [--look-at px,py,pz,tx,ty,tz,vfov] [--lens RADIUS] --out FILE.png|.ppm|.pfm|.exr
+ *              [--look-at px,py,pz,tx,ty,tz,vfov] [--lens RADIUS] [--env FILE.hdr|.pfm [--env-size N]]
+ *              --out FILE.png|.ppm|.pfm|.exr
  *
  * --scene app : the 38 spheres of App.cpp:101-122 with the reference integrator (default).
  * --obj FILE  : triangles of a Wavefront OBJ ("v" and "f" records; polygons are fanned), one grey Lambert material,
  *               mesh (wavefront) integrator; implies --philox.
+ * --env FILE  : latitude-longitude HDR panorama instead of the procedural sky (cudapt_load_environment).
  * Build: cc -std=c99 -O2 -Iinclude -o build/cudapt_cli tools/cudapt_cli.c -Lsoftware-path-tracer_b200 -lcudapt \
  *           -Wl,-rpath,'$ORIGIN/../software-path-tracer_b200'
  */
@@ -82,8 +84,8 @@ int main(int argc, char** argv) {
   cudapt_postprocess post;
   cudapt_camera cam;
   int have_cam = 0;
-  const char *out = NULL, *obj = NULL;
-  unsigned w = 640, h = 360, spp = 16;
+  const char *out = NULL, *obj = NULL, *env = NULL;
+  unsigned w = 640, h = 360, spp = 16, env_size = 256;
   cudapt_default_config(&cfg);
   cudapt_default_postprocess(&post);
   cudapt_default_camera(&cam);
@@ -93,6 +95,8 @@ int main(int argc, char** argv) {
     if (!strcmp(a, "--out")) out = nx, ++i;
     else if (!strcmp(a, "--obj")) obj = nx, ++i;
     else if (!strcmp(a, "--scene")) ++i; /* only "app" */
+    else if (!strcmp(a, "--env")) env = nx, ++i;
+    else if (!strcmp(a, "--env-size")) env_size = (unsigned)atoi(nx), ++i;
     else if (!strcmp(a, "--size")) { if (sscanf(nx, "%ux%u", &w, &h) != 2) w = h = 0; ++i; }
     else if (!strcmp(a, "--spp")) spp = (unsigned)atoi(nx), ++i;
     else if (!strcmp(a, "--bounces")) cfg.max_bounces = atoi(nx), ++i;
@@ -146,6 +150,7 @@ int main(int argc, char** argv) {
     const uint32_t n = app_spheres(sph);
     CHECK(cudapt_upload_spheres(ctx, sph, NULL, n));
   }
+  if (env) CHECK(cudapt_load_environment(ctx, env, env_size, NULL));
   CHECK(cudapt_set_postprocess(ctx, &post));
   CHECK(cudapt_render(ctx, spp));
   CHECK(cudapt_write_image(ctx, out));
