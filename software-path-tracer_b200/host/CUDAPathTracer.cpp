@@ -45,8 +45,9 @@ namespace render
 		verify(m_ctx != nullptr, "CUDA backend not initialized");
 		verify(m_scene != nullptr, "Scene not set before rendering");  // CPUPathTracer.cpp:46
 		invalidate();
-		check_status(m_ctx, cudapt_render(m_ctx, 1), "cudapt_render");  // one sample per pixel per call (:57-84)
-		m_frameCount++;
+		const uint32_t n = m_options.frames_per_render ? m_options.frames_per_render : 1u;
+		check_status(m_ctx, cudapt_render(m_ctx, n), "cudapt_render");  // one sample per pixel per call by default (:57-84)
+		m_frameCount += n;
 	}
 
 	const PathTracer::RenderResult &CUDAPathTracer::get_render_result()
@@ -54,6 +55,31 @@ namespace render
 		verify(m_frameCount > 0, "No frames rendered yet");  // CPUPathTracer.cpp:89
 		check_status(m_ctx, cudapt_resolve_rgba8(m_ctx, m_render_result.image_buffer.data()), "cudapt_resolve_rgba8");
 		return m_render_result;
+	}
+
+	void CUDAPathTracer::set_options(const Options &options)
+	{
+		m_options = options;
+		m_options_dirty = true;  // picked up by the next render(), which restarts the accumulation
+	}
+
+	// The RenderSettings fields the reference declares but never reads (Types.h:65-69).  Off: the reference's literals.
+	void CUDAPathTracer::apply_render_settings()
+	{
+		cudapt_config cfg;
+		cudapt_default_config(&cfg);
+		cudapt_postprocess post;
+		cudapt_default_postprocess(&post);
+		if (m_options.honour_render_settings)
+		{
+			cfg.max_bounces = (int32_t)m_renderSettings->getMaxBounces();
+			cfg.rr_start = (int32_t)m_renderSettings->getRussianRouletteDepth();
+			post.exposure = m_renderSettings->getExposure();
+			post.auto_exposure = m_renderSettings->getAutoExposure() ? 1 : 0;
+			post.target_luminance = m_renderSettings->getTargetLuminance();
+		}
+		check_status(m_ctx, cudapt_set_config(m_ctx, &cfg), "cudapt_set_config");
+		check_status(m_ctx, cudapt_set_postprocess(m_ctx, &post), "cudapt_set_postprocess");
 	}
 
 	// CPUPathTracer.cpp:119-161, rule for rule.
@@ -66,10 +92,12 @@ namespace render
 			restart = true;
 			needs_rebuild = true;
 		}
-		if (m_renderSettings->isDirty())
+		if (m_renderSettings->isDirty() || m_options_dirty)
 		{
 			restart = true;
+			apply_render_settings();
 			m_renderSettings->clearDirty();
+			m_options_dirty = false;
 		}
 		if (m_render_result.width != m_renderSettings->getWidth() || m_render_result.height != m_renderSettings->getHeight())
 		{

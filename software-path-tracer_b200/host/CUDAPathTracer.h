@@ -40,15 +40,34 @@ namespace render
 		// Extensions (not part of render::PathTracer): float accumulation read-back and counters.
 		cudapt_ctx *native_handle() const { return m_ctx; }
 
+		// Opt-in behaviour beyond the reference's.  The defaults reproduce CPUPathTracer exactly: it renders ONE sample
+		// per render() call (CPUPathTracer.cpp:57-84) and ignores every RenderSettings field except the resolution --
+		// max_bounces is the literal 4 (:199), roulette starts after 2 bounces (:264), the exposure lines are
+		// commented out (:101-104).
+		struct Options
+		{
+			// honour RenderSettings::getMaxBounces / getRussianRouletteDepth (integrator) and getExposure /
+			// getAutoExposure / getTargetLuminance (resolve stage); re-read whenever the settings are dirty
+			bool honour_render_settings = false;
+			// samples per pixel enqueued by one render() call (one UI frame); get_frame_count advances by this
+			uint32_t frames_per_render = 1;
+		};
+		void set_options(const Options &options);
+		const Options &get_options() const { return m_options; }
+		uint32_t get_frame_count() const { return m_frameCount; }
+
 	private:
 		void invalidate();
 		void upload_scene();
+		void apply_render_settings();
 
 		cudapt_ctx *m_ctx = nullptr;
 		std::shared_ptr<Scene> m_scene;
 		std::shared_ptr<RenderSettings> m_renderSettings;
 		PathTracer::RenderResult m_render_result;
 		uint32_t m_frameCount = 0;
+		Options m_options;
+		bool m_options_dirty = false;
 		bool m_result_pinned = false;  // m_render_result.image_buffer is registered with cudapt_host_register
 	};
 

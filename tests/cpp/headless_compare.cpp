@@ -10,6 +10,7 @@
 #include <memory>
 
 #include "CUDAPathTracer.h"
+#include "cudapt.h"
 #include "render/Log.h"
 #include "render/PathTracer.h"
 #include "render/Scene.h"
@@ -74,6 +75,42 @@ int main(int argc, char **argv)
 	std::vector<uint32_t> cpu2, gpu2;
 	drive(*cpu, w / 2, h / 2, 2, cpu2);
 	drive(*gpu, w / 2, h / 2, 2, gpu2);
+	// adapter options: honour RenderSettings (8 bounces, roulette depth 3, exposure 2) and 4 samples per render() call;
+	// the float accumulation is fingerprinted so that tests/test_gpu_adapter.py can compare it with the same render
+	// made through the C ABI directly
+	unsigned long long fnv = 1469598103934665603ull;
+	uint32_t opt_frames = 0, opt_calls = 0;
+	std::vector<uint32_t> opt_img;
+	{
+		auto gpu2p = render::create_cuda_path_tracer();
+		auto *cu = static_cast<render::CUDAPathTracer *>(gpu2p.get());
+		render::CUDAPathTracer::Options o;
+		o.honour_render_settings = true;
+		o.frames_per_render = 4;
+		cu->set_options(o);
+		auto settings = std::make_shared<render::RenderSettings>();
+		settings->setResolution(w / 2, h / 2);
+		settings->setMaxBounces(8);
+		settings->setExposure(2.0f);
+		cu->set_settings(settings);
+		cu->set_scene(make_app_scene());
+		for (int f = 0; f < 3; ++f, ++opt_calls) cu->render();
+		opt_img = cu->get_render_result().image_buffer;
+		opt_frames = cu->get_frame_count();
+		std::vector<float> acc((size_t)(w / 2) * (h / 2) * 4);
+		uint32_t fc = 0;
+		cudapt_read_accum(cu->native_handle(), acc.data(), &fc);
+		const unsigned char *b = reinterpret_cast<const unsigned char *>(acc.data());
+		for (size_t i = 0; i < acc.size() * sizeof(float); ++i) fnv = (fnv ^ b[i]) * 1099511628211ull;
+		unsigned long long fimg = 1469598103934665603ull;
+		const unsigned char *bi = reinterpret_cast<const unsigned char *>(opt_img.data());
+		for (size_t i = 0; i < opt_img.size() * 4; ++i) fimg = (fimg ^ bi[i]) * 1099511628211ull;
+		std::cout.rdbuf(old);
+		std::cout.clear();
+		std::printf("options: %ux%u, %u render() calls -> %u frames (device %u), accum fnv %016llx, image fnv %016llx\n", w / 2, h / 2, opt_calls,
+		            opt_frames, fc, fnv, fimg);
+		old = std::cout.rdbuf(nullptr);
+	}
 	std::cout.rdbuf(old);
 	std::cout.clear();
 	size_t same = 0, same2 = 0;

@@ -20,6 +20,46 @@ def test_cuda_backend_is_a_drop_in_for_the_reference_backend():
     assert "CPU Path Tracer (Embree)" in out.stdout and "CUDA Path Tracer (sm_100a)" in out.stdout
 
 
+@pytest.mark.gpu
+def test_adapter_options_equal_the_same_render_through_the_c_abi(pt, scenes):
+    """CUDAPathTracer::Options (honour RenderSettings: 8 bounces, roulette depth 3, exposure 2; 4 samples per
+    render() call): the accumulation and the image the adapter returns are those of the same settings applied
+    through the C ABI directly."""
+    import re
+    import numpy as np
+    if not os.path.exists(EXE):
+        pytest.skip("build/headless_compare not built (needs /root/reference at build time)")
+    out = subprocess.run([EXE, "256", "144", "2"], capture_output=True, text=True, timeout=600)
+    m = re.search(r"options: (\d+)x(\d+), (\d+) render\(\) calls -> (\d+) frames \(device (\d+)\), accum fnv ([0-9a-f]{16}), image fnv ([0-9a-f]{16})", out.stdout)
+    assert m, out.stdout + out.stderr[-2000:]
+    W, H, calls, frames, dev_frames = (int(m.group(k)) for k in range(1, 6))
+    assert (W, H, calls, frames, dev_frames) == (128, 72, 3, 12, 12)
+
+    def fnv(a):
+        h = 1469598103934665603
+        for b in np.ascontiguousarray(a).view(np.uint8).ravel().tolist():
+            h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        return f"{h:016x}"
+
+    sph = scenes.app_spheres()
+    ids = np.arange(2, 2 + len(sph), dtype=np.uint32)
+    with pt.PathTracer(pt.default_config(max_bounces=8, rr_start=3)) as tr:
+        tr.set_resolution(W, H)
+        tr.upload_spheres(sph, ids)
+        tr.set_postprocess(pt.default_postprocess(exposure=2.0))
+        for _ in range(3):
+            tr.render(4)
+        acc, fc = tr.read_accum()
+        img = tr.resolve_rgba8()
+    assert fc == 12 and fnv(acc) == m.group(6) and fnv(img) == m.group(7)
+    # and the options do change the picture: the reference's literals (4 bounces, exposure 1) give another image
+    with pt.PathTracer() as tr:
+        tr.set_resolution(W, H)
+        tr.upload_spheres(sph, ids)
+        tr.render(12)
+        assert fnv(tr.resolve_rgba8()) != m.group(7)
+
+
 def test_adapter_sources_mirror_the_reference_interface():
     """CPU check: the adapter overrides exactly the eight pure virtuals of render::PathTracer."""
     hdr = open(os.path.join(ROOT, "software-path-tracer_b200", "host", "CUDAPathTracer.h")).read()
