@@ -86,6 +86,32 @@ struct MeshSceneDevice {
   uint32_t n_materials;
 };
 
+// Division of a 32-bit unsigned by a divisor fixed per pass, without the 25-instruction runtime-division sequence
+// (Granlund & Montgomery 1994, the round-up form: exact for every 32-bit dividend): q = (t + ((x - t) >> sh1)) >> sh2
+// with t = mulhi(m, x), l = ceil(log2 d), m = floor(2^32 (2^l - d) / d) + 1, sh1 = min(l, 1), sh2 = max(l - 1, 0).
+// The path-id decode of the shade kernel ran two runtime divisions per path: a quarter of what every round of that
+// kernel executes (profiles/r01_notes.md).
+struct FastDiv {
+  uint32_t d, m, sh1, sh2;
+};
+inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f{d ? d : 1u, 1u, 0u, 0u};
+  uint32_t l = 0;
+  while (l < 32u && (1ull << l) < (unsigned long long)f.d) ++l;
+  f.m = (uint32_t)((((1ull << l) - f.d) << 32) / f.d + 1ull);
+  f.sh1 = l < 1u ? l : 1u;
+  f.sh2 = l > 1u ? l - 1u : 0u;
+  return f;
+}
+__host__ __device__ inline uint32_t fd_div(const FastDiv& f, uint32_t x) {
+#ifdef __CUDA_ARCH__
+  const uint32_t t = __umulhi(f.m, x);
+#else
+  const uint32_t t = (uint32_t)(((unsigned long long)f.m * x) >> 32);
+#endif
+  return (t + ((x - t) >> f.sh1)) >> f.sh2;
+}
+
 struct PassParams {
   WavefrontState st;
   MeshSceneDevice scene;
@@ -97,6 +123,7 @@ struct PassParams {
   uint32_t chunked;          // path id layout, see path_id()
   uint32_t n_slots;          // chunked layout: pixel slots = 8x8 tiles covering the image, >= n_pixels
   uint32_t slot_tiles_x;
+  FastDiv fd_slots, fd_tiles_x, fd_width, fd_pixels;  // divisions by n_slots, slot_tiles_x, im.width, n_pixels
   uint32_t first_frame;      // global 1-based frame index of sample 0 of this pass
   uint32_t frame_stride;
   float4* accum;
@@ -115,27 +142,27 @@ __host__ __device__ inline uint32_t pixel_slot(const PassParams& p, uint32_t x, 
   return (((y >> 3) * p.slot_tiles_x + (x >> 3)) << 6) | ((y & 7u) << 3) | (x & 7u);
 }
 __host__ __device__ inline bool slot_pixel(const PassParams& p, uint32_t g, uint32_t& x, uint32_t& y) {
-  const uint32_t tile = g >> 6, ty = tile / p.slot_tiles_x, tx = tile - ty * p.slot_tiles_x;
+  const uint32_t tile = g >> 6, ty = fd_div(p.fd_tiles_x, tile), tx = tile - ty * p.slot_tiles_x;
   x = (tx << 3) | (g & 7u);
   y = (ty << 3) | ((g >> 3) & 7u);
   return x < p.im.width && y < p.im.height;
 }
 __host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
   if (!p.chunked) return s * p.n_pixels + pixel;
-  const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
+  const uint32_t y = fd_div(p.fd_width, pixel), x = pixel - y * p.im.width;
   return (((s >> 5) * p.n_slots + pixel_slot(p, x, y)) << 5) | (s & 31u);
 }
 // false: the id is a padding slot of the chunked layout (no pixel)
 __host__ __device__ inline bool path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
   if (p.chunked) {
-    const uint32_t gg = id >> 5, chunk = gg / p.n_slots;
+    const uint32_t gg = id >> 5, chunk = fd_div(p.fd_slots, gg);
     uint32_t x, y;
     const bool ok = slot_pixel(p, gg - chunk * p.n_slots, x, y);
     pixel = y * p.im.width + x;
     s = (chunk << 5) | (id & 31u);
     return ok;
   }
-  s = id / p.n_pixels;
+  s = fd_div(p.fd_pixels, id);
   pixel = id - s * p.n_pixels;
   return true;
 }

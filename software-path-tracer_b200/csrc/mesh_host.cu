@@ -516,6 +516,10 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   p.n_pixels = n_pixels;
   p.n_slots = n_slots;
   p.slot_tiles_x = slot_tiles_x;
+  p.fd_slots = make_fastdiv(n_slots);
+  p.fd_tiles_x = make_fastdiv(slot_tiles_x);
+  p.fd_width = make_fastdiv(a.im.width);
+  p.fd_pixels = make_fastdiv(n_pixels);
   p.frame_stride = a.frame_stride;
   p.accum = a.accum;
   p.counters = a.counters;

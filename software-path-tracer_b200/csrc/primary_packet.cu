@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0;
 
   for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) {
-    const uint32_t chunk = task / p.n_slots, slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
+    const uint32_t chunk = fd_div(p.fd_slots, task), slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
     uint32_t x, y;
     if (!slot_pixel(p, slot, x, y) || !owns_pixel(p.im, x, y)) continue;  // warp-uniform
     const uint32_t pixel = y * p.im.width + x;

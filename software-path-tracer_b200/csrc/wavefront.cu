@@ -92,9 +92,9 @@ __global__ void __launch_bounds__(kShadeBlock) raygen_kernel(const PassParams p)
     bool live = id < total;
     uint32_t pixel = 0, x = 0, y = 0, s = 0;
     if (live) {
-      s = id / p.n_pixels;
+      s = fd_div(p.fd_pixels, id);
       pixel = id - s * p.n_pixels;
-      y = pixel / p.im.width;
+      y = fd_div(p.fd_width, pixel);
       x = pixel - y * p.im.width;
       live = owns_pixel(p.im, x, y);
     }
@@ -350,7 +350,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
 __global__ void __launch_bounds__(kShadeBlock) accumulate_kernel(const PassParams p) {
   const uint32_t stride = gridDim.x * blockDim.x;
   for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < p.n_pixels; pixel += stride) {
-    const uint32_t y = pixel / p.im.width, x = pixel - y * p.im.width;
+    const uint32_t y = fd_div(p.fd_width, pixel), x = pixel - y * p.im.width;
     if (!owns_pixel(p.im, x, y)) continue;
     float4 acc = p.accum[pixel];
     for (uint32_t s = 0; s < p.samples; ++s) {
