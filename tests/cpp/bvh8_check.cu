@@ -10,6 +10,7 @@
 
 #include "../../software-path-tracer_b200/csrc/bvh8.h"
 #include "../../software-path-tracer_b200/csrc/bvh8_traverse.cuh"
+#include "../../software-path-tracer_b200/csrc/kernels.h"
 
 using namespace cudapt;
 
@@ -173,9 +174,31 @@ static int check(const char* name, Scene sc, int n_rays, bool from_inside, bool 
   return bad;
 }
 
+// FastDiv (kernels.h): the multiply-high division of the path-id decode against the machine's own division
+static int check_fastdiv() {
+  int bad = 0;
+  uint64_t lcg = 0x9E3779B97F4A7C15ull;
+  auto rnd = [&]() { lcg = lcg * 6364136223846793005ull + 1442695040888963407ull; return (uint32_t)(lcg >> 32); };
+  std::vector<uint32_t> ds = {1u, 2u, 3u, 5u, 7u, 8u, 9u, 63u, 64u, 65u, 240u, 480u, 1920u, 3840u, 2073600u, 2088960u, 8294400u,
+                              0x7FFFFFFFu, 0x80000000u, 0x80000001u, 0xFFFFFFFEu, 0xFFFFFFFFu};
+  for (int i = 0; i < 400; ++i) ds.push_back(rnd() | 1u), ds.push_back(1u + rnd() % 5000u), ds.push_back(1u << (rnd() % 32u));
+  for (uint32_t d : ds) {
+    const cudapt::FastDiv f = cudapt::make_fastdiv(d);
+    std::vector<uint32_t> xs = {0u, 1u, d - 1u, d, d + 1u, 2u * d - 1u, 2u * d, 0x7FFFFFFFu, 0x80000000u, 0xFFFFFFFEu, 0xFFFFFFFFu};
+    for (int i = 0; i < 2000; ++i) xs.push_back(rnd());
+    for (uint32_t k = 0; k < 64u; ++k) xs.push_back((uint32_t)((uint64_t)d * ((uint64_t)rnd() % (0xFFFFFFFFull / d + 1ull))) + (k % 3u) - 1u);
+    for (uint32_t x : xs)
+      if (cudapt::fd_div(f, x) != x / d) {
+        if (++bad < 5) std::printf("fastdiv: %u / %u = %u, got %u\n", x, d, x / d, cudapt::fd_div(f, x));
+      }
+  }
+  std::printf("fastdiv: %zu divisors, %s\n", ds.size(), bad ? "MISMATCH" : "exact");
+  return bad;
+}
+
 int main(int argc, char** argv) {
   const int n_rays = argc > 1 ? std::atoi(argv[1]) : 3000;
-  int bad = 0;
+  int bad = check_fastdiv();
   bad += check("soup-2k", soup(2000, 12.f, 1.5f), n_rays, true);
   bad += check("soup-sparse", soup(300, 30.f, 0.5f), n_rays, true);
   bad += check("grid-64", grid(64), n_rays, false);
