@@ -121,6 +121,7 @@ struct PassParams {
   uint32_t n_pixels;
   uint32_t samples;          // samples of every pixel in this pass
   uint32_t chunked;          // path id layout, see path_id()
+  uint32_t explicit_q0;      // packets: queue 0 is the hit list of primary_packet.cu (kList), not the identity
   uint32_t n_slots;          // chunked layout: pixel slots = 8x8 tiles covering the image, >= n_pixels
   uint32_t slot_tiles_x;
   FastDiv fd_slots, fd_tiles_x, fd_width, fd_pixels;  // divisions by n_slots, slot_tiles_x, im.width, n_pixels
@@ -179,6 +180,7 @@ cudaError_t launch_trace_queue(const PassParams& p, const uint32_t* queue, uint3
                                cudaStream_t s);
 // primary_packet.cu: fused raygen + packet traversal of the camera rays of a pass
 bool primary_packets_enabled(const PassParams& p);
+bool primary_packet_hitlist(const PassParams& p);
 cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
                                    cudaStream_t s);
 cudaError_t launch_shade(const PassParams& p, uint32_t bounce, int queue_in, int sm_count, cudaStream_t s);

@@ -540,8 +540,10 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     // camera rays: packets (one warp = 32 samples of a pixel; fused raygen) + the per-ray kernel for the rays of
     // packets that gave up, or -- pass size not a multiple of 32 -- raygen + the per-ray kernel
     p.chunked = 0;
+    p.explicit_q0 = 0;
     const bool packets = primary_packets_enabled(p);
     p.chunked = packets ? 1u : 0u;
+    p.explicit_q0 = packets && primary_packet_hitlist(p) ? 1u : 0u;
     uint32_t* fb = p.st.counters + 4 * (size_t)(max_b + 1);  // {fall-back count, fall-back work counter}
     if (packets) {
       cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -559,6 +561,7 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
       if (e0) cudaEventRecord(e0, stream);
       R_TRY(launch_primary_packets(p, p.st.queue[1], fb, a.counting, sm_count, stream), "primary_packets");
       if (e1) cudaEventRecord(e1, stream);
+      if (p.explicit_q0) *launches += 2;  // hit-list scan + expand
     } else {
       R_TRY(launch_raygen(p, sm_count, stream), "raygen");
     }

@@ -74,6 +74,11 @@ struct PacketArgs {
   int axis_k;           // dominant axis of the camera's forward vector
   float sigma;          // its sign
   int budget;           // 3 per node step + 4 per triangle step
+  // hit list (kList): tiles of 64 packets are claimed dynamically; packets with a hit (or handed to the per-ray kernel)
+  // leave one descriptor (path id >> 5) per 32-ray chunk in the tile's region, all-sky packets are finished here
+  uint32_t* block_counter;
+  uint32_t* block_hits;   // descriptors written per tile
+  uint32_t* desc;         // tile b owns [b * 64 * kRays, (b + 1) * 64 * kRays)
 };
 
 constexpr uint32_t kNodeBytes = 96;            // staged node: 80 B + 3 scale words, padded
@@ -82,8 +87,16 @@ constexpr uint32_t kWarpSmem = kNodeBytes + kTriSlots * 48u;
 
 // kRays = rays per lane: a packet is 32 * kRays samples of one pixel (kRays consecutive 32-sample chunks), so the
 // node steps -- the larger part of a packet's cost -- are shared by more rays when the pass is deep enough.
-template <bool kCount, int kRays>
+//
+// kList (every pixel owned): the shade kernel's bounce-0 queue holds only the chunks of packets that hit something.  A
+// packet whose rays all miss -- most of an open scene's camera rays -- is FINISHED here: radiance = sky, nothing else
+// stored, never seen by the shade kernel (whose per-round bookkeeping was a quarter of the bounce-0 shade for those
+// warps, profiles/r01_notes.md).  To keep the queue in image order without a global atomic per packet, a CTA claims
+// TILES of 64 consecutive packets (one 8x8 pixel tile of one chunk group) and appends descriptors to the tile's own
+// region through a shared-memory counter; hitlist_scan / hitlist_expand then lay the regions out in tile order.
+template <bool kCount, int kRays, bool kList>
 __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6 : 4)) primary_packet_kernel(const PacketArgs a) {
+  __shared__ uint32_t s_blk, s_cnt;
   __shared__ __align__(16) unsigned char s_warp[kPacketWarps * kWarpSmem];
   __shared__ uint8_t s_lut[8 * 256];
   for (int i = threadIdx.x; i < 8 * 256; i += kPacketBlock) s_lut[i] = (uint8_t)xor_permute8((uint32_t)i & 0xFFu, (uint32_t)i >> 8);
@@ -120,12 +133,12 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   const uint32_t* node_words = opaque_ptr(reinterpret_cast<const uint32_t*>(p.scene.nodes) + (lane < 20u ? lane : 3u));
   sm_node = opaque(sm_node);
 
-  uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0;
+  uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0, sky_rays = 0;
 
-  for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) {
+  auto process = [&](const uint32_t task) {
     const uint32_t chunk = fd_div(p.fd_slots, task), slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
     uint32_t x, y;
-    if (!slot_pixel(p, slot, x, y) || !owns_pixel(p.im, x, y)) continue;  // warp-uniform
+    if (!slot_pixel(p, slot, x, y) || !owns_pixel(p.im, x, y)) return;  // warp-uniform
     const uint32_t pixel = y * p.im.width + x;
     // ---- the 32 * kRays rays (K1); ray j of a lane is sample 32 * (chunk * kRays + j) + lane ----
     const uint32_t id0 = ((chunk * kRays) * p.n_slots + slot) * 32u + lane;  // chunked path id (kernels.h path_id())
@@ -146,8 +159,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       }
       dir[j] = primary_dir(p.cam, p.im, x, y, jx, jy);
       // the origin {camera, tnear} of a camera ray is implied and queue 0 is the identity when every pixel is owned
-      // (shade_kernel, wavefront.cu): neither is stored
-      p.st.ray_d[id] = make_float4(dir[j].x, dir[j].y, dir[j].z, __int_as_float(0x7f800000));
+      // (shade_kernel, wavefront.cu): neither is stored; the direction is stored at the end, if anything still needs it
       if (p.im.part_world > 1u) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
@@ -273,6 +285,38 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       }
       if (cost > a.budget * kRays) bail = true;
     }
+    bool any_hit = true;
+    if (kList && !bail) {
+      bool mine = false;
+#pragma unroll
+      for (int j = 0; j < kRays; ++j) mine = mine || hit[j].tri != 0xFFFFFFFFu;
+      any_hit = __any_sync(kFull, mine);
+    }
+    if (!any_hit) {
+      // every ray of the packet leaves the scene: L = 0 + 1 * (sky * sky_scale), the shade kernel's miss branch for a
+      // camera ray (CPT.cpp:231-235) written out, so the bits are the same
+#pragma unroll
+      for (int j = 0; j < kRays; ++j) {
+        const f3 L = mk3(0.f, 0.f, 0.f) + mk3(1.0f, 1.0f, 1.0f) * (sky_radiance(p.ip, dir[j]) * p.ip.sky_scale);
+        p.st.L[id0 + (uint32_t)j * id_step] = make_float4(L.x, L.y, L.z, 0.f);
+      }
+      if (p.aov_prim != nullptr && chunk == 0u && lane == 0u) {  // sample 0 of the pixel is ray 0 of lane 0
+        p.aov_prim[pixel] = 0xFFFFFFFFu;
+        p.aov_t[pixel] = __int_as_float(0x7f800000);
+      }
+      sky_rays += (uint32_t)kRays;
+      done_rays += (uint32_t)kRays;
+      return;
+    }
+#pragma unroll
+    for (int j = 0; j < kRays; ++j)
+      p.st.ray_d[id0 + (uint32_t)j * id_step] = make_float4(dir[j].x, dir[j].y, dir[j].z, __int_as_float(0x7f800000));
+    if (kList) {  // one descriptor per chunk, in the tile's region
+      uint32_t pos = 0;
+      if (lane == 0) pos = atomicAdd(&s_cnt, (uint32_t)kRays);
+      pos = __shfl_sync(kFull, pos, 0);
+      if (lane < (uint32_t)kRays) a.desc[(size_t)s_blk * (64u * kRays) + pos + lane] = (id0 + lane * id_step) >> 5;
+    }
     if (!bail) {
 #pragma unroll
       for (int j = 0; j < kRays; ++j)
@@ -291,13 +335,36 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       }
       if (kCount) ++n_bail;
     }
+  };
+
+  if constexpr (kList) {
+    const uint32_t n_blocks = n_tasks >> 6;  // n_slots is a multiple of 64
+    for (;;) {
+      __syncthreads();  // the previous tile's count has been written
+      if (threadIdx.x == 0) {
+        s_blk = atomicAdd(a.block_counter, 1u);
+        s_cnt = 0u;
+      }
+      __syncthreads();
+      const uint32_t blk = s_blk;
+      if (blk >= n_blocks) break;
+      for (uint32_t t = threadIdx.x >> 5; t < 64u; t += kPacketWarps) process((blk << 6) + t);
+      __syncthreads();
+      if (threadIdx.x == 0) a.block_hits[blk] = s_cnt;
+    }
+  } else {
+    for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) process(task);
   }
-  if (p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
+  if (!kList && p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
   const uint64_t wr = warp_sum_u32(done_rays);
   if (lane == 0 && wr) {
     atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
     atomicAdd(&p.counters[kCntPacketRays], (unsigned long long)wr);
     atomicAdd(&p.counters[kCntPackets], (unsigned long long)(wr / (32u * kRays)));
+  }
+  if (kList) {
+    const uint64_t ws = warp_sum_u32(sky_rays);
+    if (lane == 0 && ws) atomicAdd(&p.counters[kCntPaths], (unsigned long long)ws);
   }
   if (kCount && lane == 0) {
     atomicAdd(&p.counters[kCntPacketNodes], (unsigned long long)n_nodes);
@@ -306,7 +373,48 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   }
 }
 
+// Hit list, step 2: exclusive scan of the descriptors per tile (one CTA; a pass has at most a few 10^5 tiles) and the
+// size of the shade kernel's bounce-0 queue.
+__global__ void __launch_bounds__(1024) hitlist_scan_kernel(const uint32_t* __restrict__ block_hits, uint32_t n_blocks,
+                                                            uint32_t* __restrict__ offsets, uint32_t* __restrict__ queue_count) {
+  __shared__ uint32_t s_sum[1024];
+  const uint32_t per = (n_blocks + 1023u) / 1024u, begin = threadIdx.x * per, end = min(begin + per, n_blocks);
+  uint32_t sum = 0;
+  for (uint32_t i = begin; i < end; ++i) sum += block_hits[i];
+  s_sum[threadIdx.x] = sum;
+  __syncthreads();
+  for (uint32_t d = 1; d < 1024u; d <<= 1) {  // Hillis-Steele inclusive scan
+    const uint32_t v = threadIdx.x >= d ? s_sum[threadIdx.x - d] : 0u;
+    __syncthreads();
+    s_sum[threadIdx.x] += v;
+    __syncthreads();
+  }
+  uint32_t run = s_sum[threadIdx.x] - sum;
+  for (uint32_t i = begin; i < end; ++i) {
+    offsets[i] = run;
+    run += block_hits[i];
+  }
+  if (threadIdx.x == 1023u) *queue_count = s_sum[1023] * 32u;
+}
+
+// Hit list, step 3: the descriptors of every tile, in tile order, expanded to the 32 path ids of their chunk.
+__global__ void __launch_bounds__(128) hitlist_expand_kernel(const uint32_t* __restrict__ desc, const uint32_t* __restrict__ block_hits,
+                                                             const uint32_t* __restrict__ offsets, uint32_t n_blocks, uint32_t region,
+                                                             uint32_t* __restrict__ queue) {
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (uint32_t b = blockIdx.x; b < n_blocks; b += gridDim.x) {
+    const uint32_t n = block_hits[b], base = offsets[b];
+    for (uint32_t k = warp; k < n; k += 4u) queue[(size_t)(base + k) * 32u + lane] = desc[(size_t)b * region + k] * 32u + lane;
+  }
+}
+
 }  // namespace
+
+// The bounce-0 hit list applies when every pixel is owned (a tile partition already keeps an explicit queue).
+bool primary_packet_hitlist(const PassParams& p) {
+  const char* e = getenv("CUDAPT_PACKET_HITLIST");  // read per pass: tests toggle it
+  return (e ? atoi(e) : 0) != 0 && p.im.part_world <= 1u && primary_packets_enabled(p);
+}
 
 // Packets apply to a pass whose sample count is a multiple of 32 (one warp = 32 samples of one pixel);
 // CUDAPT_PRIMARY_PACKETS=0 switches them off.
@@ -341,11 +449,24 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
   uint32_t grid = (uint32_t)sm_count * (rays == 1 ? 8u : (rays == 2 ? 6u : 4u));
   const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;
   if (need < grid) grid = need ? need : 1u;
-#define PK_LAUNCH(R)                                                     \
-  if (counting)                                                          \
-    primary_packet_kernel<true, R><<<grid, kPacketBlock, 0, s>>>(a);     \
-  else                                                                   \
-    primary_packet_kernel<false, R><<<grid, kPacketBlock, 0, s>>>(a)
+  // hit list: descriptors, per-tile counts and offsets live in the (still unused) shadow queue of the pass
+  const bool list = p.explicit_q0 != 0u;
+  const uint32_t n_blocks = n_tasks >> 6, n_desc = p.n_slots * chunks;
+  a.block_counter = fb_count + 2;  // free word of the fall-back counter block, zeroed with the pass's counters
+  a.desc = p.st.shadow_queue;
+  a.block_hits = p.st.shadow_queue + n_desc;
+  uint32_t* offsets = a.block_hits + n_blocks;
+#define PK_LAUNCH2(R, L)                                                    \
+  if (counting)                                                             \
+    primary_packet_kernel<true, R, L><<<grid, kPacketBlock, 0, s>>>(a);     \
+  else                                                                      \
+    primary_packet_kernel<false, R, L><<<grid, kPacketBlock, 0, s>>>(a)
+#define PK_LAUNCH(R)          \
+  if (list) {                 \
+    PK_LAUNCH2(R, true);      \
+  } else {                    \
+    PK_LAUNCH2(R, false);     \
+  }
   if (rays == 4) {
     PK_LAUNCH(4);
   } else if (rays == 2) {
@@ -354,6 +475,11 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
     PK_LAUNCH(1);
   }
 #undef PK_LAUNCH
+#undef PK_LAUNCH2
+  if (list) {
+    hitlist_scan_kernel<<<1, 1024, 0, s>>>(a.block_hits, n_blocks, offsets, p.st.counters + slot_queue_count(0));
+    hitlist_expand_kernel<<<(uint32_t)sm_count * 8u, 128, 0, s>>>(a.desc, a.block_hits, offsets, n_blocks, 64u * (uint32_t)rays, p.st.queue[0]);
+  }
   return cudaGetLastError();
 }
 

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
   // Camera rays traced as packets (p.chunked): queue 0 is the identity when every pixel is owned and is not stored,
   // and the ray origin {camera, tnear} is implied (primary_packet.cu stores it only for its fall-back rays).
   const bool camera_implied = a.bounce == 0 && p.chunked != 0u;
-  const bool ident = camera_implied && p.im.part_world <= 1u;
+  const bool ident = camera_implied && p.im.part_world <= 1u && p.explicit_q0 == 0u;
   uint32_t path_1 = i < n ? (ident ? i : qin[i]) : 0u;                             // entry of this round
   uint32_t path_2 = i + stride < n ? (ident ? i + stride : qin[i + stride]) : 0u;  // entry of the next round
   uint2 hit_1 = st.hit[path_1];

@@ -59,7 +59,8 @@ def test_packets_equal_per_ray_kernel_and_twin(pt, oracle, scenes, name, monkeyp
     a2, p2, t2, s2 = render(pt, scene, c["W"], c["H"], N, 32, cam=c["cam"], **c["kw"])
     monkeypatch.setenv("CUDAPT_PRIMARY_PACKETS", "0")
     a0, p0, t0, s0 = render(pt, scene, c["W"], c["H"], N, 32, cam=c["cam"], **c["kw"])
-    assert s1.kernel_launches == s0.kernel_launches and s1.rays == s0.rays == s2.rays and s1.paths == s0.paths
+    # (the bounce-0 hit list of the packets adds its scan and expand launches)
+    assert s1.kernel_launches in (s0.kernel_launches, s0.kernel_launches + 2) and s1.rays == s0.rays == s2.rays and s1.paths == s0.paths
     for a, p, t in ((a1, p1, t1), (a2, p2, t2)):
         assert np.array_equal(p, p0) and np.array_equal(bits(t), bits(t0))
         assert np.array_equal(bits(a), bits(a0))
@@ -141,3 +142,41 @@ def test_packets_full_size_config3_bit_identical(pt, scenes, monkeypatch):
     assert np.array_equal(p1, p0) and np.array_equal(bits(t1), bits(t0))
     assert np.array_equal(bits(a1), bits(a0))
     assert np.array_equal(bits(b1), bits(b0)) and not np.array_equal(bits(b1), bits(a1))
+
+
+@pytest.mark.parametrize("name", ["cornell", "heightfield", "heightfield_two_passes", "heightfield_env_aov"])
+def test_hit_list_bit_identical(pt, scenes, name, monkeypatch):
+    """Bounce-0 hit list (primary_packet.cu, kList): all-sky packets are finished by the packet kernel and never reach
+    the shade kernel; tiles of 64 packets are claimed dynamically.  Accumulation, primary-hit AOVs and counters must
+    equal those of the identity queue (CUDAPT_PACKET_HITLIST=0), with a budget that sends packets to the per-ray kernel
+    as well."""
+    if name == "cornell":
+        scene, W, H, N, S, cam, kw, env = scenes.cornell_box(sphere_res=8), 96, 54, 32, 32, dict(tan_half_fov=0.36), dict(max_bounces=5, jitter=1, nee=1, sky_scale=0.0, seed=5), None
+    elif name == "heightfield":
+        scene, W, H, N, S, cam, kw, env = scenes.heightfield(n_quads=96), 200, 113, 64, 64, None, dict(max_bounces=4, jitter=1, seed=7), None
+    elif name == "heightfield_two_passes":
+        scene, W, H, N, S, cam, kw, env = scenes.heightfield(n_quads=64), 97, 67, 256, 128, None, dict(max_bounces=3, jitter=1, seed=3), None
+    else:
+        scene, W, H, N, S, cam, kw, env = scenes.heightfield(n_quads=64), 128, 72, 32, 32, None, dict(max_bounces=4, jitter=0, seed=9, sky_scale=0.6), scenes.octahedral_environment(16, sun_dir=(-0.3, 0.5, 0.4))
+    out = {}
+    for budget in ("400", "12"):
+        monkeypatch.setenv("CUDAPT_PACKET_BUDGET", budget)
+        for mode in ("0", "1"):
+            monkeypatch.setenv("CUDAPT_PACKET_HITLIST", mode)
+            with pt.PathTracer(pt.default_config(rng_mode=1, samples_per_pass=S, **kw)) as tr:
+                if cam:
+                    tr.set_camera(pt.default_camera(**cam))
+                tr.set_resolution(W, H)
+                tr.upload_mesh(*scene)
+                if env is not None:
+                    tr.upload_environment(env)
+                tr.render(N)
+                acc, _ = tr.read_accum()
+                prim, t = tr.read_primary_hits()
+                st = tr.stats()
+            out[(budget, mode)] = (acc, prim, t, st)
+        (a0, p0, t0, s0), (a1, p1, t1, s1) = out[(budget, "0")], out[(budget, "1")]
+        assert np.array_equal(bits(a0), bits(a1)) and np.array_equal(p0, p1) and np.array_equal(bits(t0), bits(t1))
+        assert (s0.paths, s0.rays, s0.shade_invocations, s0.packet_rays, s0.packets) == (s1.paths, s1.rays, s1.shade_invocations, s1.packet_rays, s1.packets)
+        assert s0.paths == W * H * N and s1.kernel_launches > s0.kernel_launches
+    assert np.array_equal(bits(out[("400", "1")][0]), bits(out[("12", "1")][0]))
