@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(128) hitlist_expand_kernel(const uint32_t* __r
 // The bounce-0 hit list applies when every pixel is owned (a tile partition already keeps an explicit queue).
 bool primary_packet_hitlist(const PassParams& p) {
   const char* e = getenv("CUDAPT_PACKET_HITLIST");  // read per pass: tests toggle it
-  return (e ? atoi(e) : 0) != 0 && p.im.part_world <= 1u && primary_packets_enabled(p);
+  return (e ? atoi(e) : 1) != 0 && p.im.part_world <= 1u && primary_packets_enabled(p);
 }
 
 // Packets apply to a pass whose sample count is a multiple of 32 (one warp = 32 samples of one pixel);
