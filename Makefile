@@ -35,9 +35,26 @@ REFINC   := -I$(REF)/libs/render/include -I$(REF)/libs/render/src -I$(REF)/libs/
 host: $(PKG)/libcudapt.so oracle
 	@if [ -d $(REF)/libs/render/src ]; then $(MAKE) build/headless_compare; else echo "host: $(REF) absent, keeping prebuilt build/"; fi
 
-build/headless_compare: $(PKG)/host/CUDAPathTracer.cpp $(PKG)/host/CUDAPathTracer.h tests/cpp/headless_compare.cpp include/cudapt.h
+# The registered factory: copies of the reference's PathTracer.h / PathTracer.cpp with the GPU_CUDA
+# enumerator and case, made by applying host/reference_glue/register_gpu_cuda.patch; the adapter is copied to where
+# INTEGRATION.md puts it in the reference tree.  build/ is git-ignored: the repo carries the patch, not the copies.
+GLUE     := build/reference_glue
+$(GLUE)/PathTracer.cpp: $(PKG)/host/reference_glue/register_gpu_cuda.patch $(PKG)/host/CUDAPathTracer.h $(PKG)/host/CUDAPathTracer.cpp
+	rm -rf $(GLUE) && mkdir -p $(GLUE)/render $(GLUE)/engines/pathtracer/backends/cuda $(GLUE)/tree/libs/render/include/render $(GLUE)/tree/libs/render/src/engines/pathtracer
+	cp $(REF)/libs/render/include/render/PathTracer.h $(GLUE)/tree/libs/render/include/render/
+	cp $(REF)/libs/render/src/engines/pathtracer/PathTracer.cpp $(GLUE)/tree/libs/render/src/engines/pathtracer/
+	cd $(GLUE)/tree && patch -p1 --no-backup-if-mismatch < ../../../$(PKG)/host/reference_glue/register_gpu_cuda.patch
+	mv $(GLUE)/tree/libs/render/include/render/PathTracer.h $(GLUE)/render/PathTracer.h
+	mv $(GLUE)/tree/libs/render/src/engines/pathtracer/PathTracer.cpp $(GLUE)/PathTracer.cpp
+	rm -rf $(GLUE)/tree
+	cp $(PKG)/host/CUDAPathTracer.h $(PKG)/host/CUDAPathTracer.cpp $(GLUE)/engines/pathtracer/backends/cuda/
+
+# -I$(GLUE) comes FIRST: "render/PathTracer.h" resolves to the patched copy for every TU, the reference's own headers
+# included; the executable's create_path_tracer (patched) takes precedence over the one inside libref_render.so.
+build/headless_compare: $(GLUE)/PathTracer.cpp tests/cpp/headless_compare.cpp include/cudapt.h
 	mkdir -p build
-	$(CXX) -std=gnu++23 -O2 -w $(REFINC) -Iinclude -I$(PKG)/host -o $@ $(PKG)/host/CUDAPathTracer.cpp tests/cpp/headless_compare.cpp \
+	$(CXX) -std=gnu++23 -O2 -w -I$(GLUE) $(REFINC) -Iinclude -o $@ $(GLUE)/PathTracer.cpp \
+	    $(GLUE)/engines/pathtracer/backends/cuda/CUDAPathTracer.cpp tests/cpp/headless_compare.cpp \
 	    -L$(PKG) -lcudapt -Loracle/_ref -lref_render -Wl,-rpath,'$$ORIGIN/../$(PKG):$$ORIGIN/../oracle/_ref'
 
 # headless command-line front door, plain C over the C ABI

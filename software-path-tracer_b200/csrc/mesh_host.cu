@@ -48,6 +48,18 @@ struct MeshDevice {
   uint32_t state_paths = 0;     // capacity in paths
   uint32_t state_bounces = 0;   // counter slots allocated for this many bounces
 
+  // Copy stream and events of the double-buffered upload.  Created when the scene is BUILT (not at the first stage()),
+  // so that every render -- also those issued before the first cudapt_stage_scene -- records its last use of the
+  // buffer it read: a stage() that follows waits for that render before it overwrites the other buffer.
+  cudaError_t ensure_copy_objects() {
+    cudaError_t e;
+    if (!copy_stream && (e = cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if (!ev_copy_done && (e = cudaEventCreateWithFlags(&ev_copy_done, cudaEventDisableTiming)) != cudaSuccess) return e;
+    for (cudaEvent_t& ev : ev_last_use)
+      if (!ev && (e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+    return cudaSuccess;
+  }
+
   void free_state() {
     cudaFree(st.ray_o), cudaFree(st.ray_d), cudaFree(st.thr), cudaFree(st.L), cudaFree(st.hit);
     cudaFree(st.sh_o), cudaFree(st.sh_d), cudaFree(st.sh_c);
@@ -155,6 +167,7 @@ bool MeshScene::build_and_upload(std::string* err) {
   MH_TRY(cudaMalloc(&dev_->d_tris, tb));
   MH_TRY(cudaMalloc(&dev_->d_materials, mats.size() * sizeof(cudapt_material)));
   MH_TRY(cudaMalloc(&dev_->d_lights, std::max<size_t>(dev_->lights.size(), 1) * sizeof(uint32_t)));
+  MH_TRY(dev_->ensure_copy_objects());
   n_tris_built_ = nt;
   n_nodes_built_ = (uint32_t)bvh.nodes.size();
   accel_bytes = nb + tb;
@@ -195,6 +208,7 @@ bool MeshScene::build_on_device(cudaStream_t stream, uint64_t* launches, std::st
     dev_->pinned_bytes = nb_cap + tb;
     dev_->device_cap_nt = nt;
     dev_->device_cap_nv = nv;
+    MH_TRY(dev_->ensure_copy_objects());
   } else {
     MH_TRY(cudaStreamSynchronize(stream));
     dev_->swap_pending = false;  // a staged copy of the previous tree is dropped (its buffer is capacity-sized, see stage)
@@ -302,12 +316,11 @@ bool MeshScene::stage(cudaStream_t render_stream, std::string* err) {
     const size_t nb_alloc = dev_->device_cap_nt ? sizeof(Bvh8Node) * (size_t)(dev_->device_cap_nt / 2u + 8u) : nb;
     MH_TRY(cudaMalloc(&dev_->d_nodes_shadow, nb_alloc));
     MH_TRY(cudaMalloc(&dev_->d_tris_shadow, tb));
-    MH_TRY(cudaStreamCreateWithFlags(&dev_->copy_stream, cudaStreamNonBlocking));
-    MH_TRY(cudaEventCreateWithFlags(&dev_->ev_copy_done, cudaEventDisableTiming));
-    for (cudaEvent_t& e : dev_->ev_last_use) MH_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    // the two events start signalled
   }
-  // the shadow buffer may still be read by the last render that used it (never by the one in flight now)
+  MH_TRY(dev_->ensure_copy_objects());
+  // The shadow buffer may still be read by the last render that used it (never by the one in flight now): every
+  // render() records ev_last_use[buffer it read] (the events exist from the build on; an event that was never
+  // recorded -- the shadow buffer has not been rendered from yet -- is complete, which is then the truth).
   MH_TRY(cudaStreamWaitEvent(dev_->copy_stream, dev_->ev_last_use[dev_->current ^ 1], 0));
   MH_TRY(cudaMemcpyAsync(dev_->d_nodes_shadow, dev_->h_pinned, nb, cudaMemcpyHostToDevice, dev_->copy_stream));
   MH_TRY(cudaMemcpyAsync(dev_->d_tris_shadow, (char*)dev_->h_pinned + nb, tb, cudaMemcpyHostToDevice, dev_->copy_stream));
@@ -588,7 +601,8 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     ++*launches;
     done += s;
   }
-  if (dev_->ev_last_use[dev_->current]) R_TRY(cudaEventRecord(dev_->ev_last_use[dev_->current], stream), "event record");
+  R_TRY(dev_->ensure_copy_objects(), "copy stream / events");
+  R_TRY(cudaEventRecord(dev_->ev_last_use[dev_->current], stream), "event record");
 #undef R_TRY
   return cudaSuccess;
 }

@@ -151,9 +151,4 @@ namespace render
 		}
 		check_status(m_ctx, cudapt_upload_spheres(m_ctx, packed.data(), ids.data(), (uint32_t)spheres.size()), "cudapt_upload_spheres");
 	}
-
-	std::unique_ptr<PathTracer> create_cuda_path_tracer()
-	{
-		return std::make_unique<CUDAPathTracer>();
-	}
 }

@@ -3,8 +3,9 @@
 // Drop-in sibling of the reference's CPUPathTracer
 // (libs/render/src/engines/pathtracer/backends/cpu/CPUPathTracer.h:21-75): same eight overrides, same
 // invalidation rules (CPUPathTracer.cpp:119-161), same fail-fast error convention (render::verify).  It is
-// compiled inside the reference tree (it includes the reference's own public headers); see INTEGRATION.md for
-// the two-line factory change that registers it.
+// compiled inside the reference tree (it includes the reference's own public headers) at
+// libs/render/src/engines/pathtracer/backends/cuda/, after the factory registration patch
+// (host/reference_glue/register_gpu_cuda.patch) has been applied.
 #pragma once
 
 #include <memory>
@@ -31,9 +32,9 @@ namespace render
 		std::shared_ptr<RenderSettings> get_settings() const override { return m_renderSettings; }
 
 		std::string get_backend_name() const override { return "CUDA Path Tracer (sm_100a)"; }
-		// PathTracer::BackendType has no CUDA enumerator upstream (PathTracer.h:16-21); INTEGRATION.md appends
-		// GPU_CUDA = 3.  Until that lands the value is reported by ordinal.
-		BackendType get_backend_type() const override { return static_cast<BackendType>(3); }
+		// PathTracer::BackendType has no CUDA enumerator upstream (PathTracer.h:16-21): the registration patch
+		// (host/reference_glue/register_gpu_cuda.patch) appends GPU_CUDA and the factory case.
+		BackendType get_backend_type() const override { return BackendType::GPU_CUDA; }
 
 		const PathTracer::RenderResult &get_render_result() override;
 
@@ -71,6 +72,4 @@ namespace render
 		bool m_result_pinned = false;  // m_render_result.image_buffer is registered with cudapt_host_register
 	};
 
-	// What the factory case added in INTEGRATION.md calls.
-	std::unique_ptr<PathTracer> create_cuda_path_tracer();
 }

@@ -2,15 +2,19 @@
 // Builds the scene of App.cpp:101-122 through the reference's own Scene API and drives TWO backends through the
 // unchanged render::PathTracer interface with the five calls App makes (create :98, set_settings :129,
 // set_scene :130, render() :231, get_render_result() :232): the reference's CPUPathTracer (against the Embree
-// stand-in) and CUDAPathTracer.  Compares the RGBA8 images they return.  Test scaffolding (links oracle/_ref).
+// stand-in) and CUDAPathTracer -- BOTH created through the registered factory
+// render::PathTracer::create_path_tracer (PathTracer.cpp:11-21 with the GPU_CUDA case of
+// host/reference_glue/register_gpu_cuda.patch), which is the one line App.cpp:98 changes.  Compares the RGBA8 images
+// they return.  Test scaffolding (links oracle/_ref).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <iostream>
 #include <memory>
+#include <stdexcept>
 
-#include "CUDAPathTracer.h"
 #include "cudapt.h"
+#include "engines/pathtracer/backends/cuda/CUDAPathTracer.h"  // only for the adapter's Options (static_cast below)
 #include "render/Log.h"
 #include "render/PathTracer.h"
 #include "render/Scene.h"
@@ -69,7 +73,7 @@ int main(int argc, char **argv)
 	std::vector<uint32_t> cpu_img, gpu_img;
 	auto cpu = render::PathTracer::create_path_tracer(render::PathTracer::BackendType::CPU_EMBREE);
 	const double cpu_s = drive(*cpu, w, h, frames, cpu_img);
-	auto gpu = render::create_cuda_path_tracer();
+	auto gpu = render::PathTracer::create_path_tracer(render::PathTracer::BackendType::GPU_CUDA);
 	const double gpu_s = drive(*gpu, w, h, frames, gpu_img);
 	// resize + restart through the interface: change the resolution, render again
 	std::vector<uint32_t> cpu2, gpu2;
@@ -82,7 +86,7 @@ int main(int argc, char **argv)
 	uint32_t opt_frames = 0, opt_calls = 0;
 	std::vector<uint32_t> opt_img;
 	{
-		auto gpu2p = render::create_cuda_path_tracer();
+		auto gpu2p = render::PathTracer::create_path_tracer(render::PathTracer::BackendType::GPU_CUDA);
 		auto *cu = static_cast<render::CUDAPathTracer *>(gpu2p.get());
 		render::CUDAPathTracer::Options o;
 		o.honour_render_settings = true;
@@ -117,11 +121,24 @@ int main(int argc, char **argv)
 	for (size_t i = 0; i < cpu_img.size(); ++i) same += cpu_img[i] == gpu_img[i];
 	for (size_t i = 0; i < cpu2.size(); ++i) same2 += cpu2[i] == gpu2[i];
 	std::printf("backend cpu: %s | gpu: %s\n", cpu->get_backend_name().c_str(), gpu->get_backend_name().c_str());
+	bool unknown_throws = false;  // the factory's default branch is the reference's (PathTracer.cpp:19-20)
+	try
+	{
+		render::PathTracer::create_path_tracer(render::PathTracer::BackendType::GPU_OPTIX);
+	}
+	catch (const std::runtime_error &)
+	{
+		unknown_throws = true;
+	}
+	std::printf("factory: create_path_tracer(CPU_EMBREE) -> type %d, create_path_tracer(GPU_CUDA) -> type %d, GPU_OPTIX throws: %s\n",
+	            (int)cpu->get_backend_type(), (int)gpu->get_backend_type(), unknown_throws ? "yes" : "no");
 	std::printf("%ux%u x %d frames: identical RGBA8 pixels %zu/%zu; after resize %zu/%zu\n", w, h, frames, same, cpu_img.size(), same2,
 	            cpu2.size());
 	std::printf("wall: cpu %.3f s (%.2f Msamples/s), gpu %.4f s (%.1f Msamples/s) incl. per-frame get_render_result()\n", cpu_s,
 	            (double)w * h * frames / cpu_s / 1e6, gpu_s, (double)w * h * frames / gpu_s / 1e6);
-	const bool ok = cpu_img.size() == (size_t)w * h && same >= cpu_img.size() - cpu_img.size() / 10000 &&
+	const bool ok = cpu_img.size() == (size_t)w * h && unknown_throws &&
+	                cpu->get_backend_type() == render::PathTracer::BackendType::CPU_EMBREE &&
+	                gpu->get_backend_type() == render::PathTracer::BackendType::GPU_CUDA && same >= cpu_img.size() - cpu_img.size() / 10000 &&
 	                same2 >= cpu2.size() - cpu2.size() / 10000 - 1;
 	std::printf(ok ? "OK\n" : "MISMATCH\n");
 	return ok ? 0 : 1;

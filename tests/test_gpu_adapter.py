@@ -18,6 +18,9 @@ def test_cuda_backend_is_a_drop_in_for_the_reference_backend():
     print(out.stdout, out.stderr[-2000:])
     assert out.returncode == 0 and "OK" in out.stdout
     assert "CPU Path Tracer (Embree)" in out.stdout and "CUDA Path Tracer (sm_100a)" in out.stdout
+    # both backends came out of the REGISTERED factory (PathTracer.cpp:11-21 + the GPU_CUDA case of
+    # host/reference_glue/register_gpu_cuda.patch): enumerators 0 and 3, the default branch still throws
+    assert "factory: create_path_tracer(CPU_EMBREE) -> type 0, create_path_tracer(GPU_CUDA) -> type 3, GPU_OPTIX throws: yes" in out.stdout
 
 
 @pytest.mark.gpu
@@ -58,6 +61,23 @@ def test_adapter_options_equal_the_same_render_through_the_c_abi(pt, scenes):
         tr.upload_spheres(sph, ids)
         tr.render(12)
         assert fnv(tr.resolve_rgba8()) != m.group(7)
+
+
+def test_factory_registration_patch_is_the_two_line_delta():
+    """CPU check (needs the reference tree, i.e. runs in the build container): the patch applies cleanly to the
+    reference's PathTracer.h / PathTracer.cpp and adds exactly the enumerator, the include and the case."""
+    ref = "/root/reference/libs/render"
+    patch = os.path.join(ROOT, "software-path-tracer_b200", "host", "reference_glue", "register_gpu_cuda.patch")
+    text = open(patch).read()
+    added = [l[1:].strip() for l in text.splitlines() if l.startswith("+") and not l.startswith("+++")]
+    removed = [l[1:].strip() for l in text.splitlines() if l.startswith("-") and not l.startswith("---")]
+    assert added == ["GPU_METAL,", "GPU_CUDA", '#include "engines/pathtracer/backends/cuda/CUDAPathTracer.h"',
+                     "case BackendType::GPU_CUDA:", "return std::make_unique<render::CUDAPathTracer>();"]
+    assert removed == ["GPU_METAL"]
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not mounted")
+    r = subprocess.run(["patch", "-p1", "--dry-run", "-d", "/root/reference", "-i", patch], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
 
 
 def test_adapter_sources_mirror_the_reference_interface():

@@ -68,7 +68,7 @@ def test_device_built_tree_gives_identical_images(pt, oracle, scenes, name):
     if name in ("heightfield", "cornell"):
         tw = {("cam_" + k): v for k, v in (cam or {}).items()}
         want = oracle.TwinMesh(*scene).render(oracle.twin_params(W, H, rng_mode=1, **kw, **tw), N)[0]
-        assert float(np.all(bits(accd) == bits(want), axis=-1).mean()) >= 0.999
+        assert float(np.all(bits(accd) == bits(want), axis=-1).mean()) == 1.0
     print(f"{name}: device build {sd.accel_build_ms:.2f} ms, {sd.n_nodes} nodes | host build {sh.accel_build_ms:.2f} ms, {sh.n_nodes} nodes")
     trd.close(), trh.close()
 

@@ -33,7 +33,7 @@ def test_lens_spheres_equal_twin(pt, oracle, scenes):
     want = oracle.twin_render_spheres(oracle.twin_params(W, H, rng_mode=1, cam_lens_radius=0.15, cam_focus_distance=5.0, **kw), sph, N)[0]
     f = same_frac(acc, want)
     print(f"thin lens, spheres: {f:.5f} of pixels bit-identical")
-    assert f >= 0.999
+    assert f >= 0.9999  # sphere path: the double-precision sincos allowance of tests/test_gpu_spheres.py
     assert not np.array_equal(bits(acc), bits(pin))  # the lens does something
 
 
@@ -58,7 +58,7 @@ def test_lens_mesh_equal_twin(pt, oracle, scenes, spp_pass):
     ok = (got == widx) & (bits(t) == bits(wt))
     f = same_frac(acc, want)
     print(f"thin lens, Cornell mesh: primary {ok.mean():.5f}, accumulation {f:.5f}")
-    assert ok.mean() >= 0.9999 and f >= 0.995
+    assert ok.all() and f == 1.0  # mesh path: every pixel (tests/test_gpu_mesh.py)
 
 
 def test_lens_in_focus_plane_is_sharp(pt, scenes):

@@ -2,10 +2,11 @@
 
 The reference renders spheres only (CPUPathTracer.cpp:367-398), so this path is PARITY UNPINNED by the
 reference: the oracle is the twin, which implements DESIGN.md "Mesh integrator numerics" independently.
-Bar: primary-hit triangle ids identical and t bit-identical on >= 99.99 % of pixels; float accumulation
-bit-identical on >= 99.9 % of pixels (the spec uses only correctly rounded + - * / sqrt, so the only
-expected differences are box-culling corner cases at triangle edges), remaining pixels within the
-Monte-Carlo noise of one sample.
+Bar: EVERY pixel -- primary-hit triangle id, primary t bits, float accumulation bits.  The spec uses only
+correctly rounded + - * / sqrt and explicitly written fma in a fixed order on both sides, and the closest hit
+(smallest t, ties to the smallest caller index) does not depend on the acceleration structure: the twin's
+binary BVH and the GPU's quantised BVH8 are both conservative, so there is no allowance to state.  (The
+99.99 % allowance of the sphere path exists for its double-precision libm sincos and does not apply here.)
 """
 import numpy as np
 import pytest
@@ -34,7 +35,7 @@ def run_pair(pt, oracle, scene, W, H, N, fov=1.0, spp_pass=1, **kw):
     return tr, want, widx, wt, c
 
 
-def check_primary(tr, widx, wt, min_frac=0.9999):
+def check_primary(tr, widx, wt, min_frac=1.0):
     prim, t = tr.read_primary_hits()
     got = np.where(prim == 0xFFFFFFFF, -1, prim.astype(np.int64))
     ok = (got == widx) & (bits(t) == bits(wt))
@@ -52,11 +53,11 @@ def test_cornell_nee_matches_twin(pt, oracle, scenes):
     check_primary(tr, widx, wt)
     f = same_frac(acc, want)
     print(f"cornell accumulation bit-identical pixels: {f:.5f}")
-    assert f >= 0.999
+    assert f == 1.0
     assert abs(acc[..., :3].mean() - want[..., :3].mean()) <= 0.02 * want[..., :3].mean() + 1e-6
     st = tr.stats()
     assert st.paths == W * H * N
-    assert abs(int(st.rays) - int(c.rays)) <= 0.001 * c.rays
+    assert st.rays == c.rays and st.shade_invocations == c.shade_invocations
     assert np.array_equal(tr.resolve_rgba8(), oracle.twin_resolve_rgba8(acc, N))
     tr.close()
 
@@ -70,7 +71,7 @@ def test_heightfield_ggx_matches_twin(pt, oracle, scenes):
     check_primary(tr, widx, wt)
     f = same_frac(acc, want)
     print(f"heightfield accumulation bit-identical pixels: {f:.5f}")
-    assert f >= 0.999
+    assert f == 1.0
     tr.close()
 
 
@@ -83,7 +84,7 @@ def test_all_material_types_small(pt, oracle, scenes):
     tr, want, widx, wt, c = run_pair(pt, oracle, (v, t, m, mats), 128, 72, 5, fov=0.36, spp_pass=2, max_bounces=10, jitter=0,
                                      seed=1, nee=0, sky_scale=0.5)
     acc, _ = tr.read_accum()
-    assert same_frac(acc, want) >= 0.999
+    assert same_frac(acc, want) == 1.0
     tr.close()
 
 
@@ -179,7 +180,7 @@ def test_medium_heightfield_primary_hits_at_config_resolution(pt, oracle, scenes
     check_primary(tr, widx, wt)
     acc, _ = tr.read_accum()
     assert np.all(acc[..., 3] == 1) and np.isfinite(acc).all() and (acc[..., :3] >= 0).all()
-    assert same_frac(acc, want) >= 0.999
+    assert same_frac(acc, want) == 1.0
     tr.close()
 
 
@@ -215,7 +216,7 @@ def test_update_vertices_refit_equals_fresh_build(pt, oracle, scenes):
     assert np.array_equal(prim_refit, prim_fresh) and np.array_equal(bits(t_refit), bits(t_fresh))
     assert same_frac(before, refit) < 0.9
     want, _, _, _ = oracle.TwinMesh(v2, t, m, mats).render(oracle.twin_params(W, H, rng_mode=1, **kw), N)
-    assert same_frac(refit, want) >= 0.999
+    assert same_frac(refit, want) == 1.0
 
 
 def test_mesh_golden_fixture(pt, golden_mesh):
@@ -239,8 +240,8 @@ def test_mesh_golden_fixture(pt, golden_mesh):
     acc, prim, t, st = run(4, 2)
     got = np.where(prim == 0xFFFFFFFF, -1, prim.astype(np.int64))
     assert np.array_equal(got, g["primary_idx"]) and np.array_equal(bits(t), bits(g["primary_t"]))
-    assert same_frac(acc, g["accum4"]) >= 0.999 and abs(int(st.rays) - int(g["rays4"])) <= 0.002 * int(g["rays4"])
+    assert same_frac(acc, g["accum4"]) == 1.0 and int(st.rays) == int(g["rays4"])
     acc, _, _, st = run(32, 32)
-    assert st.packet_rays > 0 and same_frac(acc, g["accum32"]) >= 0.999
+    assert st.packet_rays > 0 and same_frac(acc, g["accum32"]) == 1.0
     acc, _, _, st = run(32, 32, lens_radius=0.05, focus_distance=4.0)
-    assert st.packet_rays == 0 and same_frac(acc, g["accum32_lens"]) >= 0.999
+    assert st.packet_rays == 0 and same_frac(acc, g["accum32_lens"]) == 1.0

@@ -70,7 +70,7 @@ def test_packets_equal_per_ray_kernel_and_twin(pt, oracle, scenes, name, monkeyp
     ok = (got == widx) & (bits(t1) == bits(wt))
     same = float(np.all(bits(a1) == bits(want), axis=-1).mean())
     print(f"{name}: packets vs twin: primary {ok.mean():.5f}, accumulation {same:.5f}")
-    assert ok.mean() >= 0.9999 and same >= 0.995
+    assert ok.all() and same == 1.0
 
 
 @pytest.mark.parametrize("rays", [1, 2, 4])
