@@ -268,6 +268,12 @@ def main():
 
     scene = build_scene(scenes, wl)
     W, H, spp = wl["w"], wl["h"], wl["spp"]
+    tile_rank, tile_world, group, n_groups = part.layout(rank, world, args.partition)
+    if tile_world > 1 and wl["kind"] == "mesh":
+        # a tile rank renders tile_world x more frames of 1/tile_world of the pixels: with the slots compacted to its own
+        # tiles (csrc/kernels.h) the same memory holds tile_world x more samples per pass
+        per_pass = int(wl["cfg"].get("samples_per_pass", 1))
+        wl["cfg"] = dict(wl["cfg"], samples_per_pass=min(256, per_pass * tile_world))
     cfg = pt.default_config(device=local_rank, **wl["cfg"])
     tr = pt.PathTracer(cfg)
     tr.set_camera(pt.default_camera(tan_half_fov=wl["fov"]))
@@ -282,7 +288,6 @@ def main():
     #   samples : rank g renders frames g+1, g+1+G, ... of every pixel                      -> render(spp)
     #   tiles   : rank g renders all G*spp frames of the 32x32 tiles it owns               -> render(spp * G)
     #   combined: T tile ranks x G/T sample groups                                          -> render(spp * T)
-    tile_rank, tile_world, group, n_groups = part.layout(rank, world, args.partition)
     frames_per_render = spp * tile_world
     if world > 1:
         if n_groups > 1:

@@ -124,6 +124,12 @@ struct PassParams {
   uint32_t explicit_q0;      // packets: queue 0 is the hit list of primary_packet.cu (kList), not the identity
   uint32_t n_slots;          // chunked layout: pixel slots = 8x8 tiles covering the image, >= n_pixels
   uint32_t slot_tiles_x;
+  // Interleaved-tile partition whose tiles are multiples of 8x8 pixels, chunked layout: the slots are COMPACTED to the
+  // 8x8 slot tiles this rank owns (owned_tiles[k] = index of the k-th owned slot tile in the image's slot-tile grid,
+  // ascending), n_slots = 64 * their number.  Every slot is then owned, so a rank's pass holds world x more samples
+  // of its own pixels in the same memory, and the camera-ray packets keep their bounce-0 hit list (primary_packet.cu).
+  const uint32_t* owned_tiles;  // nullptr: the slots cover the whole image
+  uint32_t dense;               // 1: owned_tiles is in use
   FastDiv fd_slots, fd_tiles_x, fd_width, fd_pixels;  // divisions by n_slots, slot_tiles_x, im.width, n_pixels
   uint32_t first_frame;      // global 1-based frame index of sample 0 of this pass
   uint32_t frame_stride;
@@ -143,16 +149,24 @@ __host__ __device__ inline uint32_t pixel_slot(const PassParams& p, uint32_t x, 
   return (((y >> 3) * p.slot_tiles_x + (x >> 3)) << 6) | ((y & 7u) << 3) | (x & 7u);
 }
 __host__ __device__ inline bool slot_pixel(const PassParams& p, uint32_t g, uint32_t& x, uint32_t& y) {
-  const uint32_t tile = g >> 6, ty = fd_div(p.fd_tiles_x, tile), tx = tile - ty * p.slot_tiles_x;
+#ifdef __CUDA_ARCH__
+  const uint32_t tile = p.dense ? __ldg(p.owned_tiles + (g >> 6)) : (g >> 6);
+#else
+  const uint32_t tile = g >> 6;
+#endif
+  const uint32_t ty = fd_div(p.fd_tiles_x, tile), tx = tile - ty * p.slot_tiles_x;
   x = (tx << 3) | (g & 7u);
   y = (ty << 3) | ((g >> 3) & 7u);
   return x < p.im.width && y < p.im.height;
 }
+// (pixel -> id: sample-major layout, or the chunked layout over the WHOLE image; a compacted pass goes slot -> pixel only)
 __host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
   if (!p.chunked) return s * p.n_pixels + pixel;
   const uint32_t y = fd_div(p.fd_width, pixel), x = pixel - y * p.im.width;
   return (((s >> 5) * p.n_slots + pixel_slot(p, x, y)) << 5) | (s & 31u);
 }
+// every slot of the pass belongs to this rank: no partition, or the compacted slots of one
+__host__ __device__ inline bool all_slots_owned(const PassParams& p) { return p.im.part_world <= 1u || p.dense != 0u; }
 // false: the id is a padding slot of the chunked layout (no pixel)
 __host__ __device__ inline bool path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
   if (p.chunked) {

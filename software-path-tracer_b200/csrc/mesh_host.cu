@@ -43,6 +43,10 @@ struct MeshDevice {
   uint32_t* d_material_id = nullptr;           // device build only
   LbvhScratch lbvh_scratch;                    // device build only: the builder's temporaries, kept between builds
   uint32_t device_cap_nt = 0, device_cap_nv = 0;  // sizes the device-build buffers were allocated for (0: host build)
+  // compacted tile partition (kernels.h PassParams::owned_tiles): the 8x8 slot tiles this rank owns, cached per key
+  uint32_t* d_owned_tiles = nullptr;
+  uint32_t n_owned_tiles = 0;
+  uint32_t owned_key[6] = {0, 0, 0, 0, 0, 0};  // width, height, rank, world, tile_w, tile_h
   // wavefront state
   WavefrontState st{};
   uint32_t state_paths = 0;     // capacity in paths
@@ -67,6 +71,10 @@ struct MeshDevice {
     st = WavefrontState{};
     state_paths = 0;
     state_bounces = 0;
+    cudaFree(d_owned_tiles);
+    d_owned_tiles = nullptr;
+    n_owned_tiles = 0;
+    owned_key[3] = 0;
   }
   void free_scene() {
     cudaFree(d_nodes), cudaFree(d_tris), cudaFree(d_materials), cudaFree(d_lights);
@@ -494,8 +502,42 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   }
   const uint32_t n_pixels = a.im.width * a.im.height;
   // pixel slots of the chunked path-id layout (kernels.h): the image padded to 8x8 tiles
-  const uint32_t slot_tiles_x = (a.im.width + 7u) / 8u, n_slots = slot_tiles_x * ((a.im.height + 7u) / 8u) * 64u;
+  const uint32_t slot_tiles_x = (a.im.width + 7u) / 8u, slot_tiles_y = (a.im.height + 7u) / 8u;
+  const uint32_t n_slots_full = slot_tiles_x * slot_tiles_y * 64u;
+  const uint32_t max_b = (uint32_t)a.ip.max_bounces;
+  cudaError_t e;
+  // Interleaved-tile partition with tiles that are multiples of 8x8 pixels: the passes whose camera rays are traced as
+  // packets use slots COMPACTED to the slot tiles this rank owns (list built here once per resolution / partition).
+  uint32_t n_slots_dense = 0;
+  if (a.im.part_world > 1u && a.im.tile_w % 8u == 0u && a.im.tile_h % 8u == 0u) {
+    const uint32_t key[6] = {a.im.width, a.im.height, a.im.part_rank, a.im.part_world, a.im.tile_w, a.im.tile_h};
+    if (std::memcmp(key, dev_->owned_key, sizeof(key)) != 0) {
+      std::vector<uint32_t> owned;
+      for (uint32_t ty = 0; ty < slot_tiles_y; ++ty)
+        for (uint32_t tx = 0; tx < slot_tiles_x; ++tx) {
+          const uint32_t px = (tx * 8u) / a.im.tile_w, py = (ty * 8u) / a.im.tile_h;  // cudapt_set_tile_partition's rule
+          if ((py * a.im.tiles_x + px + py) % a.im.part_world == a.im.part_rank) owned.push_back(ty * slot_tiles_x + tx);
+        }
+      cudaFree(dev_->d_owned_tiles);
+      dev_->d_owned_tiles = nullptr;
+      if ((e = cudaMalloc(&dev_->d_owned_tiles, sizeof(uint32_t) * std::max<size_t>(owned.size(), 1))) != cudaSuccess ||
+          (!owned.empty() && (e = cudaMemcpyAsync(dev_->d_owned_tiles, owned.data(), sizeof(uint32_t) * owned.size(), cudaMemcpyHostToDevice,
+                                                  stream)) != cudaSuccess) ||
+          (e = cudaStreamSynchronize(stream)) != cudaSuccess) {  // `owned` goes out of scope
+        *err = "owned-tile list";
+        return e;
+      }
+      dev_->n_owned_tiles = (uint32_t)owned.size();
+      std::memcpy(dev_->owned_key, key, sizeof(key));
+    }
+    n_slots_dense = dev_->n_owned_tiles * 64u;  // 0: this rank owns nothing -> the sparse form handles it
+  }
   uint32_t S = std::max(1u, std::min(a.samples_per_pass, a.n_frames));
+  PassParams probe;  // does a pass of S samples trace its camera rays as packets (and may therefore be compacted)?
+  probe.samples = S;
+  probe.cam = a.cam;
+  const bool first_dense = n_slots_dense != 0u && primary_packets_enabled(probe);
+  const uint32_t n_slots = first_dense ? n_slots_dense : n_slots_full;
   // 148 B of state + queues per path: keep a pass within 3/4 of the memory that is free (or already ours), and its
   // path ids within 32 bits.  The driver is asked only when the state would have to GROW: cudaMemGetInfo can take
   // milliseconds, and it sits between the render's first event and its first kernel.
@@ -509,12 +551,6 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     }
     S = (uint32_t)std::min<uint64_t>(S, 0xFFFFFFFFull / n_slots);
   }
-  const uint32_t max_b = (uint32_t)a.ip.max_bounces;
-  cudaError_t e = ensure_state(dev_, n_slots * S, max_b);
-  if (e != cudaSuccess) {
-    *err = "wavefront state allocation";
-    return e;
-  }
   PassParams p;
   p.st = dev_->st;
   p.scene.nodes = dev_->d_nodes;
@@ -527,9 +563,8 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   p.im = a.im;
   p.ip = a.ip;
   p.n_pixels = n_pixels;
-  p.n_slots = n_slots;
   p.slot_tiles_x = slot_tiles_x;
-  p.fd_slots = make_fastdiv(n_slots);
+  p.owned_tiles = dev_->d_owned_tiles;
   p.fd_tiles_x = make_fastdiv(slot_tiles_x);
   p.fd_width = make_fastdiv(a.im.width);
   p.fd_pixels = make_fastdiv(n_pixels);
@@ -546,6 +581,19 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   while (done < a.n_frames) {
     const uint32_t s = std::min(S, a.n_frames - done);
     p.samples = s;
+    // slots of this pass: compacted to the owned tiles when its camera rays go as packets under a tile partition
+    p.dense = (n_slots_dense != 0u && primary_packets_enabled(p)) ? 1u : 0u;
+    p.n_slots = p.dense ? n_slots_dense : n_slots_full;
+    p.fd_slots = make_fastdiv(p.n_slots);
+    if ((uint64_t)p.n_slots * s > 0xFFFFFFFFull) {
+      *err = "pass too large for 32-bit path ids";
+      return cudaErrorInvalidValue;
+    }
+    if ((e = ensure_state(dev_, p.n_slots * s, max_b)) != cudaSuccess) {  // grows only
+      *err = "wavefront state allocation";
+      return e;
+    }
+    p.st = dev_->st;
     p.first_frame = a.first_frame + done * a.frame_stride;
     p.aov_prim = done == 0 ? a.aov_prim : nullptr;
     p.aov_t = done == 0 ? a.aov_t : nullptr;

@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   auto process = [&](const uint32_t task) {
     const uint32_t chunk = fd_div(p.fd_slots, task), slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
     uint32_t x, y;
-    if (!slot_pixel(p, slot, x, y) || !owns_pixel(p.im, x, y)) return;  // warp-uniform
+    if (!slot_pixel(p, slot, x, y) || (!p.dense && !owns_pixel(p.im, x, y))) return;  // warp-uniform
     const uint32_t pixel = y * p.im.width + x;
     // ---- the 32 * kRays rays (K1); ray j of a lane is sample 32 * (chunk * kRays + j) + lane ----
     const uint32_t id0 = ((chunk * kRays) * p.n_slots + slot) * 32u + lane;  // chunked path id (kernels.h path_id())
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       dir[j] = primary_dir(p.cam, p.im, x, y, jx, jy);
       // the origin {camera, tnear} of a camera ray is implied and queue 0 is the identity when every pixel is owned
       // (shade_kernel, wavefront.cu): neither is stored; the direction is stored at the end, if anything still needs it
-      if (p.im.part_world > 1u) {
+      if (!kList && !all_slots_owned(p)) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
         base = __shfl_sync(kFull, base, 0);
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   } else {
     for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) process(task);
   }
-  if (!kList && p.im.part_world <= 1u && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
+  if (!kList && all_slots_owned(p) && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
   const uint64_t wr = warp_sum_u32(done_rays);
   if (lane == 0 && wr) {
     atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
@@ -410,10 +410,11 @@ __global__ void __launch_bounds__(128) hitlist_expand_kernel(const uint32_t* __r
 
 }  // namespace
 
-// The bounce-0 hit list applies when every pixel is owned (a tile partition already keeps an explicit queue).
+// The bounce-0 hit list applies when every slot of the pass is owned: no partition, or the compacted slots of a tile
+// partition (kernels.h); a sparse partition keeps an explicit queue built with one atomic per packet.
 bool primary_packet_hitlist(const PassParams& p) {
   const char* e = getenv("CUDAPT_PACKET_HITLIST");  // read per pass: tests toggle it
-  return (e ? atoi(e) : 1) != 0 && p.im.part_world <= 1u && primary_packets_enabled(p);
+  return (e ? atoi(e) : 1) != 0 && all_slots_owned(p) && primary_packets_enabled(p);
 }
 
 // Packets apply to a pass whose sample count is a multiple of 32 (one warp = 32 samples of one pixel);

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
   // Camera rays traced as packets (p.chunked): queue 0 is the identity when every pixel is owned and is not stored,
   // and the ray origin {camera, tnear} is implied (primary_packet.cu stores it only for its fall-back rays).
   const bool camera_implied = a.bounce == 0 && p.chunked != 0u;
-  const bool ident = camera_implied && p.im.part_world <= 1u && p.explicit_q0 == 0u;
+  const bool ident = camera_implied && all_slots_owned(p) && p.explicit_q0 == 0u;
   uint32_t path_1 = i < n ? (ident ? i : qin[i]) : 0u;                             // entry of this round
   uint32_t path_2 = i + stride < n ? (ident ? i + stride : qin[i + stride]) : 0u;  // entry of the next round
   uint2 hit_1 = st.hit[path_1];
@@ -349,12 +349,30 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM) shade_kernel(c
 // ---- K6: add the pass's per-path radiance to the accumulation buffer, in sample order (CPT.cpp:77-80) --
 __global__ void __launch_bounds__(kShadeBlock) accumulate_kernel(const PassParams p) {
   const uint32_t stride = gridDim.x * blockDim.x;
+  if (p.chunked) {
+    // chunked layout: slot by slot (8 neighbouring pixels of a row per 8 threads); the ids of a slot are 32 * n_slots apart
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < p.n_slots; g += stride) {
+      uint32_t x, y;
+      if (!slot_pixel(p, g, x, y) || (!p.dense && !owns_pixel(p.im, x, y))) continue;
+      const uint32_t pixel = y * p.im.width + x;
+      float4 acc = p.accum[pixel];
+      for (uint32_t s = 0; s < p.samples; ++s) {
+        const float4 l = p.st.L[(((s >> 5) * p.n_slots + g) << 5) | (s & 31u)];
+        acc.x += l.x;
+        acc.y += l.y;
+        acc.z += l.z;
+        acc.w += 1.0f;
+      }
+      p.accum[pixel] = acc;
+    }
+    return;
+  }
   for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < p.n_pixels; pixel += stride) {
     const uint32_t y = fd_div(p.fd_width, pixel), x = pixel - y * p.im.width;
     if (!owns_pixel(p.im, x, y)) continue;
     float4 acc = p.accum[pixel];
     for (uint32_t s = 0; s < p.samples; ++s) {
-      const float4 l = p.st.L[path_id(p, pixel, s)];
+      const float4 l = p.st.L[s * p.n_pixels + pixel];
       acc.x += l.x;
       acc.y += l.y;
       acc.z += l.z;
@@ -384,7 +402,7 @@ cudaError_t launch_shade(const PassParams& p, uint32_t bounce, int queue_in, int
 }
 
 cudaError_t launch_accumulate(const PassParams& p, int sm_count, cudaStream_t s) {
-  accumulate_kernel<<<grid_for(p.n_pixels, sm_count, kShadeBlock), kShadeBlock, 0, s>>>(p);
+  accumulate_kernel<<<grid_for(p.chunked ? p.n_slots : p.n_pixels, sm_count, kShadeBlock), kShadeBlock, 0, s>>>(p);
   return cudaGetLastError();
 }
 

@@ -180,3 +180,37 @@ def test_hit_list_bit_identical(pt, scenes, name, monkeypatch):
         assert (s0.paths, s0.rays, s0.shade_invocations, s0.packet_rays, s0.packets) == (s1.paths, s1.rays, s1.shade_invocations, s1.packet_rays, s1.packets)
         assert s0.paths == W * H * N and s1.kernel_launches > s0.kernel_launches
     assert np.array_equal(bits(out[("400", "1")][0]), bits(out[("12", "1")][0]))
+
+
+@pytest.mark.parametrize("case", ["cornell", "heightfield_ragged", "many_ranks"])
+def test_compacted_tile_partition_keeps_packets_and_hit_list(pt, scenes, case, monkeypatch):
+    """Interleaved-tile partition with tiles that are multiples of 8x8 pixels: a pass whose camera rays go as packets
+    compacts its slots to the rank's own slot tiles (csrc/kernels.h PassParams::owned_tiles), so it keeps the bounce-0
+    hit list and holds world x more samples in the same memory.  The ranks' buffers must still sum to the one-context
+    image BIT FOR BIT (zeros elsewhere), AOVs and counters must add up, and tiles that are NOT multiples of 8 (the
+    sparse form: explicit queue, one atomic per packet) must give the same image."""
+    monkeypatch.delenv("CUDAPT_PACKET_HITLIST", raising=False)
+    monkeypatch.delenv("CUDAPT_PRIMARY_PACKETS", raising=False)
+    if case == "cornell":
+        scene, W, H, N, S, cam, kw, G, tile = scenes.cornell_box(sphere_res=8), 96, 54, 64, 64, dict(tan_half_fov=0.36), dict(max_bounces=5, jitter=1, nee=1, sky_scale=0.0, seed=5), 3, (16, 8)
+    elif case == "heightfield_ragged":  # width and height not multiples of 8 or of the tile: padded slots at the borders
+        scene, W, H, N, S, cam, kw, G, tile = scenes.heightfield(n_quads=64), 203, 117, 96, 32, None, dict(max_bounces=4, jitter=1, seed=7), 2, (32, 32)
+    else:  # more ranks than tile columns: some ranks own very little
+        scene, W, H, N, S, cam, kw, G, tile = scenes.heightfield(n_quads=48), 72, 40, 32, 32, None, dict(max_bounces=3, jitter=1, seed=3), 8, (24, 16)
+    full, fprim, ft, fst = render(pt, scene, W, H, N, S, cam=cam, **kw)
+    for tw, th in (tile, (tile[0] + 4, tile[1] + 2)):  # compacted form, then a tile size that forces the sparse form
+        total = np.zeros_like(full)
+        prim = np.full((H, W), 0xFFFFFFFF, np.uint32)
+        tt = np.full((H, W), np.inf, np.float32)
+        paths = rays = packet_rays = 0
+        for r in range(G):
+            a, p_, t_, st = render(pt, scene, W, H, N, S, cam=cam, part=(r, G, tw, th), **kw)
+            ty, tx = np.meshgrid(np.arange(H) // th, np.arange(W) // tw, indexing="ij")
+            own = (ty * ((W + tw - 1) // tw) + tx + ty) % G == r
+            assert np.all(a[~own] == 0) and np.all(a[own][:, 3] == N)
+            total += a
+            prim[own], tt[own] = p_[own], t_[own]
+            paths, rays, packet_rays = paths + st.paths, rays + st.rays, packet_rays + st.packet_rays
+        assert np.array_equal(bits(total), bits(full))
+        assert np.array_equal(prim, fprim) and np.array_equal(bits(tt), bits(ft))
+        assert (paths, rays) == (fst.paths, fst.rays) and packet_rays > 0.9 * W * H * N
