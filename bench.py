@@ -231,6 +231,8 @@ def main():
                     help="N > 1: how a step's work is split over the ranks (SURVEY 8e): sample ranges (B, default: best "
                          "balance), interleaved 32x32 tiles (A: per-pixel sums in single-GPU order), or tile groups x "
                          "sample ranges")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling for any workload: the workload's samples per pixel are the TOTAL over the ranks (c5 always is)")
     ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],
                     help="N > 1 read-back tail: 'fused' = one reduce-scatter+resolve+gather kernel per rank over NVLink "
                          "peer memory (cudapt_reduce_resolve_peers); 'nccl' = NCCL reduce of the float buffer to rank 0")
@@ -245,7 +247,7 @@ def main():
         wl["spp"] = args.spp
     if args.spp_pass:
         wl["cfg"] = dict(wl["cfg"], samples_per_pass=args.spp_pass)
-    strong = bool(wl.get("strong"))
+    strong = bool(wl.get("strong")) or args.strong
     if strong:  # total work fixed: every rank renders its share of the samples
         wl["spp"] = max(1, wl["spp"] // world)
     scenes = importlib.import_module("software-path-tracer_b200.scenes")
