@@ -227,10 +227,11 @@ def main():
     ap.add_argument("--no-parity-check", action="store_true", help="N > 1: skip the check of the assembled image after the timed regions")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
     ap.add_argument("--spp-pass", type=int, default=0, help="override samples per wavefront pass (debug)")
-    ap.add_argument("--partition", default="samples", choices=["samples", "tiles", "combined"],
-                    help="N > 1: how a step's work is split over the ranks (SURVEY 8e): sample ranges (B, default: best "
-                         "balance), interleaved 32x32 tiles (A: per-pixel sums in single-GPU order), or tile groups x "
-                         "sample ranges")
+    ap.add_argument("--partition", default="tiles", choices=["samples", "tiles", "combined"],
+                    help="N > 1: how a step's work is split over the ranks (SURVEY 8e): interleaved 32x32 tiles (A, default: "
+                         "per-pixel sums in single-GPU order, so the assembled image is BIT-IDENTICAL to one GPU's; the slots of "
+                         "a pass are compacted to the rank's own tiles, csrc/kernels.h), sample ranges (B: every rank renders "
+                         "the whole image for its own frames), or tile groups x sample ranges")
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling for any workload: the workload's samples per pixel are the TOTAL over the ranks (c5 always is)")
     ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],

@@ -400,7 +400,7 @@ inline void consider(const Mesh& m, uint32_t prim, V3 o, V3 d, float tnear, Mesh
   }
 }
 
-inline bool slab(const Node& nd, V3 o, V3 inv, float tnear, float tmax) {
+inline bool slab(const Node& nd, V3 o, V3 inv, float tnear, float tmax, float* entry = nullptr) {
   float t0 = (nd.lo[0] - o.x) * inv.x, t1 = (nd.hi[0] - o.x) * inv.x;
   float tmin = std::min(t0, t1), tmx = std::max(t0, t1);
   t0 = (nd.lo[1] - o.y) * inv.y, t1 = (nd.hi[1] - o.y) * inv.y;
@@ -408,6 +408,7 @@ inline bool slab(const Node& nd, V3 o, V3 inv, float tnear, float tmax) {
   t0 = (nd.lo[2] - o.z) * inv.z, t1 = (nd.hi[2] - o.z) * inv.z;
   tmin = std::max(tmin, std::min(t0, t1)), tmx = std::min(tmx, std::max(t0, t1));
   tmin = std::max(tmin, tnear * 0.5f);
+  if (entry) *entry = tmin;
   // conservative: widen the exit distance (Ize 2013) so grazing rays are not culled before the exact test
   return tmin <= std::min(tmx * 1.0000005f + 1e-6f, tmax);
 }
@@ -419,25 +420,49 @@ inline V3 safe_inv(V3 d) {
   return v3(f(d.x), f(d.y), f(d.z));
 }
 
+// Front-to-back: both children are tested when their parent is opened and the nearer one is visited first, so that
+// the shrinking best.t culls the farther one (the result -- smallest t, ties to the smallest index -- does not depend
+// on the order; the work does).
 MeshHit closest_bvh(const Mesh& m, V3 o, V3 d, float tnear, Counters* cnt) {
   MeshHit best{-1, std::numeric_limits<float>::infinity()};
   if (m.nodes.empty()) return best;
   const V3 inv = safe_inv(d);
-  uint32_t stack[96];
+  struct Entry {
+    uint32_t node;
+    float t;
+  };
+  Entry stack[128];
   int sp = 0;
-  stack[sp++] = 0;
+  if (cnt) ++cnt->nodes;
+  float troot;
+  if (!slab(m.nodes[0], o, inv, tnear, best.t, &troot)) return best;
+  stack[sp++] = {0, troot};
   while (sp) {
-    const Node& nd = m.nodes[stack[--sp]];
-    if (cnt) ++cnt->nodes;
-    if (!slab(nd, o, inv, tnear, best.t)) continue;
+    const Entry e = stack[--sp];
+    if (e.t > best.t) continue;  // culled by a hit found since it was pushed
+    const Node& nd = m.nodes[e.node];
     if (nd.count) {
       for (uint32_t i = 0; i < nd.count; ++i) {
         if (cnt) ++cnt->tris;
         consider(m, m.prims[nd.left + i], o, d, tnear, best);
       }
-    } else {
-      stack[sp++] = nd.left;
-      stack[sp++] = nd.left + 1;
+      continue;
+    }
+    float ta, tb;
+    if (cnt) cnt->nodes += 2;
+    const bool ha = slab(m.nodes[nd.left], o, inv, tnear, best.t, &ta), hb = slab(m.nodes[nd.left + 1], o, inv, tnear, best.t, &tb);
+    if (ha && hb) {
+      if (ta <= tb) {
+        stack[sp++] = {nd.left + 1, tb};
+        stack[sp++] = {nd.left, ta};
+      } else {
+        stack[sp++] = {nd.left, ta};
+        stack[sp++] = {nd.left + 1, tb};
+      }
+    } else if (ha) {
+      stack[sp++] = {nd.left, ta};
+    } else if (hb) {
+      stack[sp++] = {nd.left + 1, tb};
     }
   }
   return best;
@@ -516,15 +541,81 @@ void build_bvh(Mesh& m) {
       m.nodes[j.node] = nd;
       continue;
     }
-    int axis = 0;
-    if (chi[1] - clo[1] > chi[axis] - clo[axis]) axis = 1;
-    if (chi[2] - clo[2] > chi[axis] - clo[axis]) axis = 2;
-    const uint32_t mid = j.begin + cnt / 2;
-    std::nth_element(m.prims.begin() + j.begin, m.prims.begin() + mid, m.prims.begin() + j.end,
-                     [&](uint32_t a, uint32_t b) {
-                       const float ca = cen[3 * (size_t)a + axis], cb = cen[3 * (size_t)b + axis];
-                       return ca < cb || (ca == cb && a < b);
-                     });
+    // Binned surface-area heuristic (16 bins per axis on the centroid bounds, all three axes); the median of the
+    // widest axis when no split plane separates the centroids.  The tree only shapes the WORK of a query -- any
+    // conservative tree returns the same closest hit -- so this is about giving the CPU arm a fair structure.
+    constexpr int kBins = 16;
+    auto half_area = [](const float* l, const float* h) {
+      const float dx = h[0] - l[0], dy = h[1] - l[1], dz = h[2] - l[2];
+      return dx * dy + dy * dz + dz * dx;
+    };
+    float best_cost = INFINITY, best_pos = 0.f;
+    int best_axis = -1;
+    for (int axis = 0; axis < 3; ++axis) {
+      const float ext = chi[axis] - clo[axis];
+      if (!(ext > 0.f)) continue;
+      struct Bin {
+        float lo[3], hi[3];
+        uint32_t n;
+      } bins[kBins];
+      for (Bin& b : bins) {
+        for (int k = 0; k < 3; ++k) b.lo[k] = INFINITY, b.hi[k] = -INFINITY;
+        b.n = 0;
+      }
+      const float scale = (float)kBins / ext;
+      for (uint32_t i = j.begin; i < j.end; ++i) {
+        const size_t p = m.prims[i];
+        int b = (int)((cen[3 * p + axis] - clo[axis]) * scale);
+        b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+        for (int k = 0; k < 3; ++k) {
+          bins[b].lo[k] = std::min(bins[b].lo[k], blo[3 * p + k]);
+          bins[b].hi[k] = std::max(bins[b].hi[k], bhi[3 * p + k]);
+        }
+        ++bins[b].n;
+      }
+      float right_area[kBins];
+      uint32_t right_n[kBins];
+      float rl[3] = {INFINITY, INFINITY, INFINITY}, rh[3] = {-INFINITY, -INFINITY, -INFINITY};
+      uint32_t rn = 0;
+      for (int b = kBins - 1; b > 0; --b) {
+        for (int k = 0; k < 3; ++k) rl[k] = std::min(rl[k], bins[b].lo[k]), rh[k] = std::max(rh[k], bins[b].hi[k]);
+        rn += bins[b].n;
+        right_area[b] = rn ? half_area(rl, rh) : 0.f;
+        right_n[b] = rn;
+      }
+      float ll[3] = {INFINITY, INFINITY, INFINITY}, lh[3] = {-INFINITY, -INFINITY, -INFINITY};
+      uint32_t ln = 0;
+      for (int b = 0; b + 1 < kBins; ++b) {
+        for (int k = 0; k < 3; ++k) ll[k] = std::min(ll[k], bins[b].lo[k]), lh[k] = std::max(lh[k], bins[b].hi[k]);
+        ln += bins[b].n;
+        if (ln == 0 || right_n[b + 1] == 0) continue;
+        const float cost = half_area(ll, lh) * (float)ln + right_area[b + 1] * (float)right_n[b + 1];
+        if (cost < best_cost) best_cost = cost, best_axis = axis, best_pos = clo[axis] + (float)(b + 1) / scale;
+      }
+    }
+    uint32_t mid = j.begin + cnt / 2;
+    if (best_axis >= 0) {
+      const int axis = best_axis;
+      const float scale = (float)kBins / (chi[axis] - clo[axis]);
+      const int split_bin = (int)((best_pos - clo[axis]) * scale + 0.5f);
+      auto it = std::partition(m.prims.begin() + j.begin, m.prims.begin() + j.end, [&](uint32_t a) {
+        int b = (int)((cen[3 * (size_t)a + axis] - clo[axis]) * scale);
+        b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
+        return b < split_bin;
+      });
+      mid = (uint32_t)(it - m.prims.begin());
+    }
+    if (best_axis < 0 || mid == j.begin || mid == j.end) {  // coincident centroids (or a degenerate partition): median
+      int axis = 0;
+      if (chi[1] - clo[1] > chi[axis] - clo[axis]) axis = 1;
+      if (chi[2] - clo[2] > chi[axis] - clo[axis]) axis = 2;
+      mid = j.begin + cnt / 2;
+      std::nth_element(m.prims.begin() + j.begin, m.prims.begin() + mid, m.prims.begin() + j.end,
+                       [&](uint32_t a, uint32_t b) {
+                         const float ca = cen[3 * (size_t)a + axis], cb = cen[3 * (size_t)b + axis];
+                         return ca < cb || (ca == cb && a < b);
+                       });
+    }
     nd.left = (uint32_t)m.nodes.size();
     nd.count = 0;
     m.nodes[j.node] = nd;
