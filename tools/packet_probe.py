@@ -32,6 +32,7 @@ for b in budgets:
         st = tr.stats()
         if not counting:
             print(f"{name} spp {spp} budget {b}: render {st.last_render_ms:.3f} ms, trace launches {st.last_trace_ms:.3f} ms, packets {st.last_packet_ms:.3f} ms", flush=True)
+            print(f"closest-hit rays traced by the per-ray kernel in one pass: {st.rays - st.shadow_rays - st.packet_rays}", flush=True)
         else:
             npk = max(st.packets + st.packet_bails, 1)
             print(f"   per packet: nodes {st.packet_nodes / npk:.2f} tris {st.packet_tris / npk:.2f} bails {st.packet_bails / npk:.4f}"
