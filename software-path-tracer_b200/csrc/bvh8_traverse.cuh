@@ -147,12 +147,7 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
   // the mask by one funnel shift per child: 9 alu-pipe instructions per node instead of FSETP + SEL + IADD3 = 20
   // (the node test is alu-pipe bound, profiles/r01_notes.md).  cmin > 0 always (tmin > 0 or tiny negative, see
   // the callers), so cmax - cmin is never -0 for cmin <= cmax, and no operand is NaN.
-#if defined(__CUDA_ARCH__) && defined(PT_NODE_FADD)
-  // Variant: the clamps against tmin / tmax_w become two more subtractions (fma pipe) whose sign bits are OR-ed into
-  // the interval's (one LOP3): per child 2 FMNMX3 + LOP3 + SHF on the alu pipe instead of 2 FMNMX3 + 2 FMNMX + SHF.
-#define PT_RECORD(BIT)                                                                                                   \
-  hits = __funnelshift_l(__float_as_uint(cmax - cmin) | __float_as_uint(tmax_w - cmin) | __float_as_uint(cmax - tmin), hits, 1);
-#elif defined(__CUDA_ARCH__)
+#ifdef __CUDA_ARCH__
 #define PT_RECORD(BIT) hits = __funnelshift_l(__float_as_uint(cmax - cmin), hits, 1);
 #else
 #define PT_RECORD(BIT) if (cmin <= cmax) hits |= 1u << (BIT);
@@ -164,15 +159,6 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
     const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
     const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
-#if defined(__CUDA_ARCH__) && defined(PT_NODE_FADD)
-#define PT_CMINMAX                                          \
-  const float cmin = fmaxf(fmaxf(t0x, t0y), t0z);           \
-  const float cmax = fminf(fminf(t1x, t1y), t1z);
-#else
-#define PT_CMINMAX                                                   \
-  const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));       \
-  const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));
-#endif
 #define PT_CHILD(J)                                                                \
     {                                                                              \
       const float t0x = fmaf(byte_as_biased_float<J>(nearx, magic), adjx, o0x);    \
@@ -181,13 +167,13 @@ __host__ __device__ __forceinline__ uint32_t intersect_node(const uint4 w0, cons
       const float t1x = fmaf(byte_as_biased_float<J>(farx, magic), adjx, o1x);     \
       const float t1y = fmaf(byte_as_biased_float<J>(fary, magic), adjy, o1y);     \
       const float t1z = fmaf(byte_as_biased_float<J>(farz, magic), adjz, o1z);     \
-      PT_CMINMAX                                                                   \
+      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                 \
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax_w));               \
       /* empty slots (inverted boxes) may pass; imask / tri_valid keep them out */ \
       PT_RECORD(4 * half + J)                                                      \
     }
     PT_CHILD(3) PT_CHILD(2) PT_CHILD(1) PT_CHILD(0)
 #undef PT_CHILD
-#undef PT_CMINMAX
   }
 #undef PT_RECORD
 #ifdef __CUDA_ARCH__
