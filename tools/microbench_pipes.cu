@@ -57,6 +57,27 @@ __global__ void __launch_bounds__(256) k(float* out, unsigned seed, float fa) {
       b0 = b0 * seed + w; b1 = b1 * seed + w; b2 = b2 * seed + w; b3 = b3 * seed + w;
       a4 = __uint_as_float(b0); a5 = __uint_as_float(b1); a6 = __uint_as_float(b2); a7 = __uint_as_float(b3);
       (void)u;
+    } else if (MODE == 8) {  // 4 FFMA2 (fma.rn.f32x2: two FMAs per lane and instruction) on four register pairs
+#define F2(lo, hi) { unsigned long long x, y, z, r; \
+      asm volatile("mov.b64 %0, {%1, %2};" : "=l"(x) : "f"(lo), "f"(hi)); \
+      asm volatile("mov.b64 %0, {%1, %1};" : "=l"(y) : "f"(fa)); \
+      asm volatile("mov.b64 %0, {%1, %1};" : "=l"(z) : "f"(1.0f)); \
+      asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(x), "l"(y), "l"(z)); \
+      asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(r)); }
+      F2(a0, a1) F2(a2, a3) F2(a4, a5) F2(a6, a7)
+    } else if (MODE == 9) {  // 4 PRMT + 2 FFMA2 (the box test's flavour with paired FMAs)
+      unsigned v0, v1, v2, v3;
+      asm volatile("prmt.b32 %0, %1, %2, 0x7540;" : "=r"(v0) : "r"(w), "r"(m));
+      asm volatile("prmt.b32 %0, %1, %2, 0x7541;" : "=r"(v1) : "r"(w), "r"(m));
+      asm volatile("prmt.b32 %0, %1, %2, 0x7542;" : "=r"(v2) : "r"(w), "r"(m));
+      asm volatile("prmt.b32 %0, %1, %2, 0x7543;" : "=r"(v3) : "r"(w), "r"(m));
+#define F2Q(q0, q1, lo, hi) { unsigned long long x, y, z, r; \
+      asm volatile("mov.b64 %0, {%1, %2};" : "=l"(x) : "r"(q0), "r"(q1)); \
+      asm volatile("mov.b64 %0, {%1, %1};" : "=l"(y) : "f"(fa)); \
+      asm volatile("mov.b64 %0, {%1, %2};" : "=l"(z) : "f"(lo), "f"(hi)); \
+      asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(x), "l"(y), "l"(z)); \
+      asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(r)); }
+      F2Q(v0, v1, a0, a1) F2Q(v2, v3, a2, a3)
     }
   }
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 + __uint_as_float(w);
@@ -89,5 +110,7 @@ int main() {
   run<5>("2 PRMT + 4 FHFMA", 6, d);
   run<6>("4 FFMA + 4 FMNMX", 8, d);
   run<7>("8 IMAD", 8, d);
+  run<8>("4 FFMA2 (= 8 FMA)", 4, d);
+  run<9>("4 PRMT + 2 FFMA2", 6, d);
   return 0;
 }
