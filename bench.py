@@ -601,8 +601,23 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
         n_sph = len(scene["spheres"])
         flops = (st.rays / max(st.paths, 1)) * (25.0 * n_sph + 12.0) + (st.shade_invocations / max(st.paths, 1)) * 90.0
         achieved = alg_bytes / (render_ms * 1e-3) / 1e9
-        return {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "note": note,
+        # counters of render_spheres_kernel from an `ncu --set full` capture of this build (tools/run_c1.sh ->
+        # tools/make_trace_ncu_json.py), stamped with a hash of the kernel's sources like the traversal kernel's
+        issue, traffic = None, None
+        spath = os.path.join(ROOT, "profiles", "spheres_kernel_ncu.json")
+        if os.path.exists(spath):
+            cap = json.load(open(spath))
+            fresh = cap.get("build_hash") == kernel_build_hash(SPHERES_SOURCES)
+            if fresh and cap.get("c1"):
+                issue = dict(cap["c1"], capture="profiles/spheres_kernel_ncu.json", commit=cap.get("commit"), build_hash_matches=True)
+                traffic = cap["c1"].get("dram_bytes_per_launch")
+            else:
+                issue = {"capture": "profiles/spheres_kernel_ncu.json", "commit": cap.get("commit"), "build_hash_matches": bool(fresh),
+                         "note": "STALE: the kernel's sources changed since the capture; figures withheld"}
+        return {"bound": "issue", "kernel": "render_spheres_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": traffic, "issue": issue, "peak_source": peak_src,
+                "note": note + ". 'achieved' / 'peak' / 'frac' are the contract's algorithmic bytes over the HBM copy peak (0.3 %: "
+                               "nothing here is memory bound); 'issue' holds the counters that bind it",
                 "compute": {"flops_per_path": flops, "achieved_tflops": flops * n_px * spp / (render_ms * 1e-3) / 1e12,
                             "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12}}
     paths = max(st.paths, 1)
@@ -685,18 +700,27 @@ def roofline(tr, pt, wl, scene, st, render_ms, hbm_peak, peak_src):
                     "triangles per ray of the per-ray kernel (camera rays finished by packets excluded)"}
 
 
-def trace_build_hash():
-    """sha256 over the sources that make the per-ray traversal kernel (and the flags it is compiled with): the stamp of
-    profiles/trace_kernel_ncu.json."""
+TRACE_SOURCES = ("trace_bvh.cu", "bvh8_traverse.cuh", "bvh8.h", "common.cuh", "kernels.h")
+SPHERES_SOURCES = ("spheres.cu", "common.cuh", "kernels.h")
+
+
+def kernel_build_hash(files):
+    """sha256 over the sources that make a kernel (and the flags it is compiled with): the stamp of an ncu capture under
+    profiles/."""
     import hashlib
     h = hashlib.sha256()
     csrc = os.path.join(ROOT, "software-path-tracer_b200", "csrc")
-    for f in ("trace_bvh.cu", "bvh8_traverse.cuh", "bvh8.h", "common.cuh", "kernels.h"):
+    for f in files:
         h.update(open(os.path.join(csrc, f), "rb").read())
     for line in open(os.path.join(ROOT, "Makefile")):
         if line.startswith("NVFLAGS") or line.startswith("            -"):
             h.update(line.encode())
     return h.hexdigest()[:16]
+
+
+def trace_build_hash():
+    """Stamp of profiles/trace_kernel_ncu.json: the per-ray traversal kernel's sources and flags."""
+    return kernel_build_hash(TRACE_SOURCES)
 
 
 if __name__ == "__main__":

@@ -47,7 +47,30 @@ def rows_of(rep):
     return res
 
 
+def spheres(rep):
+    """profiles/spheres_kernel_ncu.json from a capture of render_spheres_kernel (tools/run_c1.sh)."""
+    r = next(x for x in rows_of(rep) if "render_spheres" in x["kernel"])
+    out = {"_source": "tools/run_c1.sh (ncu --set full --clock-control none -k regex:render_spheres -c 1 on `bench.py --workload c1`) "
+                      "-> tools/make_trace_ncu_json.py spheres=<rep>: one 16-frame launch of the configs[0] scene",
+           "build_hash": bench.kernel_build_hash(bench.SPHERES_SOURCES),
+           "commit": subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip(),
+           "c1": {"launch_us": r["dur_us"], "warp_instructions": r["inst"], "dram_bytes_per_launch": r["dram_read"] + r["dram_write"],
+                  **{k: r[k] for k in ("issue_slot_utilisation_pct", "lanes_per_instruction", "alu_pipe_pct", "fma_pipe_pct",
+                                       "warps_active_pct", "l1_hit_pct", "l2_hit_pct", "dram_pct_of_peak") if k in r}}}
+    json.dump(out, open(os.path.join(ROOT, "profiles", "spheres_kernel_ncu.json"), "w"), indent=1)
+    print(json.dumps(out, indent=1))
+
+
 def main():
+    args = []
+    for a in sys.argv[1:]:
+        if a.startswith("spheres="):
+            spheres(a.split("=", 1)[1])
+        else:
+            args.append(a)
+    if not args:
+        return
+    sys.argv[1:] = args
     out = {"_source": "tools/run_traffic.sh (ncu --set full --clock-control none, -k regex:trace_kernel, one pass of "
                       "tools/packet_probe.py with camera-ray packets on) -> tools/make_trace_ncu_json.py. dram_bytes_per_ray = "
                       "(dram__bytes_read.sum + dram__bytes_write.sum) summed over the captured closest-hit launches / the rays "
