@@ -21,16 +21,20 @@ print(round(j['value'],1),'Msamples/s',round(j['ms_per_step'],3),'ms; e2e',round
   python bench.py --impl reference --workload c3 --steps 20 --warmup 3 > gpurun_out/${tag}_ref_c3.json 2>&1
   tail -c 300 gpurun_out/${tag}_ref_c3.json
   ;;
-b)
+b)   # (gpurun copies back at most 64 MiB: the c4 capture goes in part b2)
   for w in c3 c4; do WORKLOAD=$w TAG=$tag bash tools/run_launches2.sh | tail -12; done
-  WORKLOADS="c3 c4" bash tools/run_traffic.sh
+  WORKLOADS="c3" bash tools/run_traffic.sh
   mv gpurun_out/traffic_c3.ncu-rep gpurun_out/${tag}_traffic_c3.ncu-rep; mv gpurun_out/traffic_c3.log gpurun_out/${tag}_traffic_c3.log
-  mv gpurun_out/traffic_c4.ncu-rep gpurun_out/${tag}_traffic_c4.ncu-rep; mv gpurun_out/traffic_c4.log gpurun_out/${tag}_traffic_c4.log
   ncu --set full --clock-control none --import-source on -k regex:primary_packet -c 1 -f -o gpurun_out/${tag}_packets_c3 \
     python tools/packet_probe.py c3 64 400 > gpurun_out/ncu_pk.log 2>&1
   ncu --set full --clock-control none --import-source on -k regex:shade_kernel -c 2 -f -o gpurun_out/${tag}_shade_c3 \
     python tools/packet_probe.py c3 64 400 > gpurun_out/ncu_sh.log 2>&1
-  ls -la gpurun_out/*.ncu-rep
+  ls -la gpurun_out/*.ncu-rep; du -sh gpurun_out
+  ;;
+b2)
+  WORKLOADS="c4" bash tools/run_traffic.sh
+  mv gpurun_out/traffic_c4.ncu-rep gpurun_out/${tag}_traffic_c4.ncu-rep; mv gpurun_out/traffic_c4.log gpurun_out/${tag}_traffic_c4.log
+  ls -la gpurun_out/*.ncu-rep; du -sh gpurun_out
   ;;
 c)
   python bench.py --workload c5 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_scale1_c5_strong_none.json 2> gpurun_out/${tag}_scale1_c5.err
