@@ -503,22 +503,30 @@ def main():
             tr.wait_download()
             tr.resolve_rgba8_async(host_rgba[k & 1])          # resolve kernel + D2H, not waited for here
 
+    # The e2e loop is timed on the HOST clock, so one scheduling hiccup of the host (a short step makes K steps a few
+    # tens of ms) can swamp it.  The K-step loop is therefore run three times when it is short (< 2 s) and the MEDIAN
+    # run is reported, with all runs listed in `e2e.runs_ms`; a long loop (c4, c5) runs once.
     e2e_step()
     tr.wait_download()
-    sync_all()
-    t0 = time.perf_counter()
-    e2e_marks = []
-    for k in range(args.steps):
-        e2e_step(k, first=(k == 0), last=(k == args.steps - 1))   # exactly one scene upload per step
-        e2e_marks.append(time.perf_counter())
-    tr.wait_download()                                            # the last image is on the host
-    sync_all()
-    if os.environ.get("BENCH_DEBUG"):
-        print(f"[rank {rank}] e2e step s {[round(b - a, 4) for a, b in zip([t0] + e2e_marks[:-1], e2e_marks)]}", file=sys.stderr, flush=True)
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = world * paths_per_step * args.steps / float(e2e_s.item()) / 1e6
+    e2e_runs = []
+    while True:
+        sync_all()
+        t0 = time.perf_counter()
+        e2e_marks = []
+        for k in range(args.steps):
+            e2e_step(k, first=(k == 0), last=(k == args.steps - 1))   # exactly one scene upload per step
+            e2e_marks.append(time.perf_counter())
+        tr.wait_download()                                            # the last image is on the host
+        sync_all()
+        if os.environ.get("BENCH_DEBUG"):
+            print(f"[rank {rank}] e2e step s {[round(b - a, 4) for a, b in zip([t0] + e2e_marks[:-1], e2e_marks)]}", file=sys.stderr, flush=True)
+        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
+        if world > 1:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)   # every rank sees the same time, so all leave the loop together
+        e2e_runs.append(float(e2e_s.item()))
+        if len(e2e_runs) >= 3 or e2e_runs[0] >= 2.0:
+            break
+    e2e_value = world * paths_per_step * args.steps / sorted(e2e_runs)[len(e2e_runs) // 2] / 1e6
 
     # the read-back tail alone (N > 1): CUDA events on the library's stream, max over ranks
     tail_info = None
@@ -565,7 +573,8 @@ def main():
                    if world > 1 else "single GPU"},
         "mrays_per_s": value * rays_per_path, "rays_per_path": rays_per_path,
         "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(scene_bytes),
-                "d2h_bytes_per_step": int(n_px * 4)},
+                "d2h_bytes_per_step": int(n_px * 4), "runs_ms": [round(1e3 * t, 3) for t in e2e_runs],
+                "note": f"median of {len(e2e_runs)} host-clock timed runs of {args.steps} steps each"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roof,
