@@ -232,6 +232,7 @@ def main():
                          "per-pixel sums in single-GPU order, so the assembled image is BIT-IDENTICAL to one GPU's; the slots of "
                          "a pass are compacted to the rank's own tiles, csrc/kernels.h), sample ranges (B: every rank renders "
                          "the whole image for its own frames), or tile groups x sample ranges")
+    ap.add_argument("--tile", type=int, default=32, help="N > 1, tile partitions: edge of the square interleaved tiles in pixels (multiple of 8)")
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling for any workload: the workload's samples per pixel are the TOTAL over the ranks (c5 always is)")
     ap.add_argument("--tail", default="fused", choices=["fused", "nccl"],
@@ -296,7 +297,7 @@ def main():
         if n_groups > 1:
             tr.set_frame_range(*part.frame_range(group, n_groups))
         if tile_world > 1:
-            tr.set_tile_partition(tile_rank, tile_world, 32, 32)
+            tr.set_tile_partition(tile_rank, tile_world, args.tile, args.tile)
 
     stream = torch.cuda.ExternalStream(tr.stream_handle, device=local_rank)
     n_px = W * H
@@ -404,20 +405,23 @@ def main():
             denom = np.maximum(np.abs(single), 1e-3)
             max_rel = float((np.abs(merged - single) / denom).max())
             img_vs_single = float((rgba == rgba_single).mean())
+            chan = lambda w: np.stack([(w >> sh) & 0xFF for sh in (24, 16, 8, 0)], -1).astype(np.int32)
+            max_lsb = int(np.abs(chan(rgba) - chan(rgba_single)).max())
             tiles_only = n_groups == 1
             ok = (same_merge and img_vs_merge == 1.0) if fused else (close_merge and img_vs_merge >= 0.9999)
             if tiles_only:
                 ok = ok and same_single == 1.0 and img_vs_single == 1.0
             else:
-                ok = ok and max_rel <= 2e-5 and img_vs_single >= 0.9999
+                ok = ok and max_rel <= 2e-5 and img_vs_single >= 0.999 and max_lsb <= 1
             out = {"mode": args.partition, "tail": args.tail, "frames_per_pixel": int(total), "ok": bool(ok),
                    "float_sums_bit_identical_to_rank_ordered_host_merge": same_merge,
                    "rgba8_equal_to_resolve_of_host_merge": img_vs_merge,
                    "pixels_bit_identical_to_single_context": same_single, "max_rel_diff_vs_single_context": max_rel,
-                   "rgba8_equal_to_single_context": img_vs_single,
+                   "rgba8_equal_to_single_context": img_vs_single, "rgba8_max_channel_difference_lsb": max_lsb,
                    "bar": ("tiles: float sums and RGBA8 bit-identical to ONE context rendering the same frames" if tiles_only else
                            "sample ranges: float sums within 2e-5 relative of ONE context rendering the same frames (re-association of "
-                           f"{total} adds), RGBA8 equal on >= 99.99 % of the words") +
+                           f"{total} adds), RGBA8 within 1 LSB per channel everywhere and equal on >= 99.9 % of the words (a sum that lands "
+                           "within 4e-6 relative of an 8-bit truncation boundary may flip it)") +
                           ("; fused tail bit-identical to the rank-ordered host merge" if fused else "; NCCL reduce allclose to the host merge")}
         sync_all()
         return out
@@ -565,7 +569,7 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "name": wl["name"], "width": W, "height": H, "spp_per_gpu": spp,
                    "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
-                   "partition": ("one process per GPU; " + {"samples": "sample ranges per rank", "tiles": "interleaved 32x32 tiles per rank",
+                   "partition": ("one process per GPU; " + {"samples": "sample ranges per rank", "tiles": f"interleaved {args.tile}x{args.tile} tiles per rank",
                                                             "combined": f"{tile_world} tile ranks x {n_groups} sample groups"}[args.partition] + "; " +
                                  ("fused tail every step: one reduce-scatter + resolve + gather kernel per rank over "
                                   "NVLink peer memory (CUDA IPC), rank-ordered sums" if fused else

@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 N=${N:-2}; tag=${TAG:-r02}; port=29600
 for run in ${RUNS:-c3:weak:samples}; do
   IFS=: read w mode part <<< "$run"
-  extra=""; [ "$mode" = strong ] && [ "$w" != c5 ] && extra="--strong"
+  extra="${EXTRA:-}"; [ "$mode" = strong ] && [ "$w" != c5 ] && extra="$extra --strong"
   out=gpurun_out/${tag}_scale${N}_${w}_${mode}_${part}.json
   port=$((port + 1))
   if [ "$N" = 1 ]; then
