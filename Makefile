@@ -6,7 +6,7 @@ CSRC     := $(PKG)/csrc
 NVFLAGS  := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
             -fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
             -Xcompiler -fPIC,-O2,-ffp-contract=off -Xptxas -v
-CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace_bvh.cu $(CSRC)/wavefront.cu $(CSRC)/post.cu $(CSRC)/refit.cu $(CSRC)/primary_packet.cu $(CSRC)/lbvh_build.cu
+CU       := $(CSRC)/api.cu $(CSRC)/spheres.cu $(CSRC)/mesh_host.cu $(CSRC)/trace_bvh.cu $(CSRC)/wavefront.cu $(CSRC)/post.cu $(CSRC)/refit.cu $(CSRC)/primary_packet.cu $(CSRC)/lbvh_build.cu $(CSRC)/static_scratch.cu
 HDR      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cudapt.h
 OBJ      := $(CU:.cu=.o) $(CSRC)/bvh_build.o $(CSRC)/env_load.o
 

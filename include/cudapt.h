@@ -296,6 +296,25 @@ int cudapt_ipc_export(cudapt_ctx* ctx, void* accum_handle, void* rgba_handle);
 int cudapt_ipc_open(cudapt_ctx* ctx, const void* handle, void** device_ptr);
 int cudapt_ipc_close(cudapt_ctx* ctx, void* device_ptr);
 
+/* ---- allocation-free entry point (no counterpart in the reference) ---- */
+/* The auto-exposure reduction of cudapt_postprocess.auto_exposure (log-average luminance of accum / frame_count ->
+ * exposure = target_luminance / exp(mean log luminance)) for callers that cannot call cudaMalloc: code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it.  It allocates NOTHING (no cudaMalloc / cudaFree, no allocating
+ * library routine): its scratch -- one partial sum per 1024 pixels -- lives in a file-scope `static __device__` array of
+ * 64 KB that every GPU loading the library holds until exit (csrc/static_scratch.cu), which bounds the image size:
+ * n_pixels <= CUDAPT_STATIC_MAX_PIXELS (16 777 216 = two 4K frames); larger sizes are rejected with CUDAPT_ERR_INVALID.
+ * The caller passes the input and the output: accum_device = float4[n_pixels] in the memory of `device` (e.g.
+ * cudapt_accum_device_ptr), exposure_device_out = one float in device memory; the two kernels are enqueued on `stream`
+ * (a cudaStream_t; NULL = the default stream) and the call returns without synchronising.  The result equals, bit for
+ * bit, what cudapt_get_exposure reports after an auto-exposure cudapt_resolve_rgba8 of the same buffer.
+ * Every call on a device shares the array, which keeps the last call's contents (nothing in it needs clearing: each
+ * call overwrites and reads exactly its own [0, n) partials); calls that OVERLAP on the GPU -- different streams without
+ * an ordering between them -- race on it.  The first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress): make that call outside a graph capture.  Error text through cudapt_last_error(NULL). */
+#define CUDAPT_STATIC_MAX_PIXELS 16777216u
+int cudapt_auto_exposure_static(int device, const void* accum_device, uint32_t n_pixels, uint32_t frame_count,
+                                float target_luminance, float* exposure_device_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,7 +82,9 @@ EXPORTS = [
     "cudapt_reduce_resolve_peers", "cudapt_rgba_device_ptr", "cudapt_download_rgba8", "cudapt_ipc_export",
     "cudapt_ipc_open", "cudapt_ipc_close",
     "cudapt_upload_environment", "cudapt_load_environment", "cudapt_convert_environment", "cudapt_default_postprocess", "cudapt_set_postprocess", "cudapt_get_exposure", "cudapt_write_image",
+    "cudapt_auto_exposure_static",
 ]
+STATIC_MAX_PIXELS = 16777216  # CUDAPT_STATIC_MAX_PIXELS
 
 _lib = None
 
@@ -159,6 +161,8 @@ def load_library() -> ctypes.CDLL:
     lib.cudapt_set_postprocess.argtypes = [vp, ctypes.POINTER(PostProcess)]
     lib.cudapt_get_exposure.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     lib.cudapt_write_image.argtypes = [vp, ctypes.c_char_p]
+    lib.cudapt_auto_exposure_static.argtypes = [i32, vp, u32, u32, ctypes.c_float, vp, vp]
+    lib.cudapt_auto_exposure_static.restype = i32
     _lib = lib
     return lib
 
@@ -216,6 +220,18 @@ def convert_environment(path: str, size: int = 256) -> np.ndarray:
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def auto_exposure_static(device: int, accum_device_ptr: int, n_pixels: int, frame_count: int, target_luminance: float,
+                         exposure_device_ptr: int, stream: int = 0):
+    """cudapt_auto_exposure_static: the allocation-free auto-exposure reduction (device pointers in and out, enqueued on
+    `stream`).  Raises CudaptError with the library's text on a non-zero status."""
+    lib = load_library()
+    rc = lib.cudapt_auto_exposure_static(int(device), ctypes.c_void_p(int(accum_device_ptr)), int(n_pixels), int(frame_count),
+                                         float(target_luminance), ctypes.c_void_p(int(exposure_device_ptr)),
+                                         ctypes.c_void_p(int(stream)) if stream else None)
+    if rc != 0:
+        raise CudaptError(rc, (lib.cudapt_last_error(None) or b"").decode())
 
 
 class PathTracer:

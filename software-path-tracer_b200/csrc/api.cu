@@ -198,6 +198,11 @@ void free_spheres(cudapt_ctx* ctx) {
 
 }  // namespace
 
+// for entry points that live in other translation units and have no context (csrc/static_scratch.cu)
+namespace cudapt {
+void set_thread_error(const char* text) { g_create_error = text ? text : ""; }
+}  // namespace cudapt
+
 extern "C" {
 
 int cudapt_abi_version(void) { return CUDAPT_ABI_VERSION; }
