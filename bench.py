@@ -277,7 +277,7 @@ def main():
         # a tile rank renders tile_world x more frames of 1/tile_world of the pixels: with the slots compacted to its own
         # tiles (csrc/kernels.h) the same memory holds tile_world x more samples per pass
         per_pass = int(wl["cfg"].get("samples_per_pass", 1))
-        wl["cfg"] = dict(wl["cfg"], samples_per_pass=min(256, per_pass * tile_world))
+        wl["cfg"] = dict(wl["cfg"], samples_per_pass=min(1024, per_pass * tile_world))
     cfg = pt.default_config(device=local_rank, **wl["cfg"])
     tr = pt.PathTracer(cfg)
     tr.set_camera(pt.default_camera(tan_half_fov=wl["fov"]))

@@ -80,8 +80,10 @@ typedef struct cudapt_config {
   uint32_t seed;             /* Philox key word 1 */
   int32_t jitter;            /* default 0: sub-pixel jitter (Philox mode only); 0 = reference corner sampling */
   int32_t nee;               /* default 0: next-event estimation on emissive triangles (mesh integrator) */
-  int32_t samples_per_pass;  /* default 1, <= 256: samples of every pixel traced together by the wavefront (136 B of path
-                                state per sample and pixel: large passes amortise the near-empty tail bounces) */
+  int32_t samples_per_pass;  /* default 1, <= 1024: samples of every pixel traced together by the wavefront (136 B of path
+                                state per sample and pixel: large passes amortise the near-empty tail bounces; a pass
+                                that does not fit 3/4 of the free device memory is shrunk; under a tile partition a pass
+                                holds only the rank's own pixels, so `world` x more samples fit the same memory) */
 } cudapt_config;
 
 typedef struct cudapt_stats {

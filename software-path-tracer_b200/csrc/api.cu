@@ -100,7 +100,7 @@ int fail(cudapt_ctx* ctx, int code, const char* fmt, ...) {
 
 bool valid_config(const cudapt_config& c) {
   return c.max_bounces >= 1 && c.max_bounces <= 64 && c.rr_start >= 0 && c.samples_per_pass >= 1 &&
-         c.samples_per_pass <= 256 && (c.rng_mode == CUDAPT_RNG_REFERENCE_PCG || c.rng_mode == CUDAPT_RNG_PHILOX);
+         c.samples_per_pass <= 1024 && (c.rng_mode == CUDAPT_RNG_REFERENCE_PCG || c.rng_mode == CUDAPT_RNG_PHILOX);
 }
 
 CameraParams camera_params(const cudapt_camera& c) {

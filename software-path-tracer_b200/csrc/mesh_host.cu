@@ -71,6 +71,10 @@ struct MeshDevice {
     st = WavefrontState{};
     state_paths = 0;
     state_bounces = 0;
+  }
+  // NOT part of free_state(): render() builds the list and then grows the path state (ensure_state -> free_state), and
+  // the list only depends on (resolution, partition), which its key already covers
+  void free_partition() {
     cudaFree(d_owned_tiles);
     d_owned_tiles = nullptr;
     n_owned_tiles = 0;
@@ -127,6 +131,7 @@ void MeshScene::release() {
   if (dev_) {
     dev_->free_state();
     dev_->free_scene();
+    dev_->free_partition();
     delete dev_;
     dev_ = nullptr;
   }

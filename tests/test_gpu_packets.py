@@ -214,3 +214,22 @@ def test_compacted_tile_partition_keeps_packets_and_hit_list(pt, scenes, case, m
         assert np.array_equal(bits(total), bits(full))
         assert np.array_equal(prim, fprim) and np.array_equal(bits(tt), bits(ft))
         assert (paths, rays) == (fst.paths, fst.rays) and packet_rays > 0.9 * W * H * N
+
+
+def test_pass_of_512_samples_under_a_tile_partition(pt, scenes):
+    """samples_per_pass up to 1024: what a tile rank of an 8-GPU run uses (512 frames of its own pixels in ONE pass, 4 rays
+    per lane).  Same image, bit for bit, as 32-sample passes of one context over the whole image."""
+    scene = scenes.heightfield(n_quads=64)
+    W, H, N, G = 128, 72, 512, 8
+    kw = dict(max_bounces=4, jitter=1, seed=19)
+    full, fprim, ft, fst = render(pt, scene, W, H, N, 32, **kw)
+    total = np.zeros_like(full)
+    paths = 0
+    for r in range(G):
+        a, _, _, st = render(pt, scene, W, H, N, 512, part=(r, G, 32, 32), **kw)
+        total += a
+        paths += st.paths
+        assert st.packet_rays > 0 or st.paths == 0
+    assert np.array_equal(bits(total), bits(full)) and paths == fst.paths == W * H * N
+    with pytest.raises(pt.CudaptError):
+        pt.PathTracer(pt.default_config(rng_mode=1, samples_per_pass=1025))
