@@ -120,7 +120,8 @@ struct PassParams {
   IntegratorParams ip;
   uint32_t n_pixels;
   uint32_t samples;          // samples of every pixel in this pass
-  uint32_t chunked;          // path id layout, see path_id()
+  uint32_t chunked;          // path id layout, see path_id(): 0 sample-major, 1 chunked (32 k samples), 2 slot-major (1..16 samples)
+  uint32_t s_shift;          // ids of one slot and chunk are 2^s_shift apart from the next slot's: 5 (chunked == 1) or log2(samples) (== 2)
   uint32_t explicit_q0;      // packets: queue 0 is the hit list of primary_packet.cu (kList), not the identity
   uint32_t n_slots;          // chunked layout: pixel slots = 8x8 tiles covering the image, >= n_pixels
   uint32_t slot_tiles_x;
@@ -163,18 +164,27 @@ __host__ __device__ inline bool slot_pixel(const PassParams& p, uint32_t g, uint
 __host__ __device__ inline uint32_t path_id(const PassParams& p, uint32_t pixel, uint32_t s) {
   if (!p.chunked) return s * p.n_pixels + pixel;
   const uint32_t y = fd_div(p.fd_width, pixel), x = pixel - y * p.im.width;
-  return (((s >> 5) * p.n_slots + pixel_slot(p, x, y)) << 5) | (s & 31u);
+  return ((((s >> 5) * p.n_slots + pixel_slot(p, x, y)) << p.s_shift) | (s & ((1u << p.s_shift) - 1u)));  // = slot_sample_id()
 }
 // every slot of the pass belongs to this rank: no partition, or the compacted slots of one
 __host__ __device__ inline bool all_slots_owned(const PassParams& p) { return p.im.part_world <= 1u || p.dense != 0u; }
+// Path id of (slot g, sample s) in the two slot-based layouts.  chunked == 2, SLOT-MAJOR (passes of 1, 2, 4, 8 or 16
+// samples): id = g * S + s, so 32 consecutive ids = 32 / S neighbouring pixels of an 8x8 tile row block x S samples = one
+// camera-ray packet of SEVERAL pixels (primary_packet.cu, kMini) -- what a viewer that renders 1 sample per call, or a
+// strong-scaled rank with a few samples per pixel, gets.
+// ONE formula serves both: with s_shift = 5 it is the chunked id, and in the slot-major layout s < 32, so the chunk term
+// vanishes and (g << s_shift) | s is left.
+__host__ __device__ inline uint32_t slot_sample_id(const PassParams& p, uint32_t g, uint32_t s) {
+  return (((s >> 5) * p.n_slots + g) << p.s_shift) | (s & ((1u << p.s_shift) - 1u));
+}
 // false: the id is a padding slot of the chunked layout (no pixel)
 __host__ __device__ inline bool path_decode(const PassParams& p, uint32_t id, uint32_t& pixel, uint32_t& s) {
-  if (p.chunked) {
-    const uint32_t gg = id >> 5, chunk = fd_div(p.fd_slots, gg);
+  if (p.chunked) {  // both slot-based layouts: in the slot-major one id >> s_shift < n_slots, so chunk = 0 falls out
+    const uint32_t gg = id >> p.s_shift, chunk = fd_div(p.fd_slots, gg);
     uint32_t x, y;
     const bool ok = slot_pixel(p, gg - chunk * p.n_slots, x, y);
     pixel = y * p.im.width + x;
-    s = (chunk << 5) | (id & 31u);
+    s = (chunk << 5) | (id & ((1u << p.s_shift) - 1u));
     return ok;
   }
   s = fd_div(p.fd_pixels, id);
@@ -194,6 +204,8 @@ cudaError_t launch_trace_queue(const PassParams& p, const uint32_t* queue, uint3
                                cudaStream_t s);
 // primary_packet.cu: fused raygen + packet traversal of the camera rays of a pass
 bool primary_packets_enabled(const PassParams& p);
+// the pass size alone allows packets: a multiple of 32 samples (one pixel per packet) or 1, 2, 4, 8, 16 (several pixels)
+bool primary_packet_shape(uint32_t samples);
 bool primary_packet_hitlist(const PassParams& p);
 cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
                                    cudaStream_t s);

@@ -541,6 +541,8 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
   PassParams probe;  // does a pass of S samples trace its camera rays as packets (and may therefore be compacted)?
   probe.samples = S;
   probe.cam = a.cam;
+  probe.im = a.im;
+  probe.dense = n_slots_dense != 0u ? 1u : 0u;  // if the pass can be compacted it will be
   const bool first_dense = n_slots_dense != 0u && primary_packets_enabled(probe);
   const uint32_t n_slots = first_dense ? n_slots_dense : n_slots_full;
   // 148 B of state + queues per path: keep a pass within 3/4 of the memory that is free (or already ours), and its
@@ -587,7 +589,8 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     const uint32_t s = std::min(S, a.n_frames - done);
     p.samples = s;
     // slots of this pass: compacted to the owned tiles when its camera rays go as packets under a tile partition
-    p.dense = (n_slots_dense != 0u && primary_packets_enabled(p)) ? 1u : 0u;
+    p.dense = n_slots_dense != 0u ? 1u : 0u;  // tentatively: packets of 1..16 samples need every slot owned
+    p.dense = primary_packets_enabled(p) ? p.dense : 0u;
     p.n_slots = p.dense ? n_slots_dense : n_slots_full;
     p.fd_slots = make_fastdiv(p.n_slots);
     if ((uint64_t)p.n_slots * s > 0xFFFFFFFFull) {
@@ -607,8 +610,12 @@ cudaError_t MeshScene::render(const MeshRenderArgs& a, cudaStream_t stream, uint
     // packets that gave up, or -- pass size not a multiple of 32 -- raygen + the per-ray kernel
     p.chunked = 0;
     p.explicit_q0 = 0;
+    p.s_shift = 0;
     const bool packets = primary_packets_enabled(p);
-    p.chunked = packets ? 1u : 0u;
+    // path-id layout: chunked for passes of 32 k samples (one pixel per packet), slot-major for 1..16 (several pixels)
+    p.chunked = packets ? (s % 32u == 0u ? 1u : 2u) : 0u;
+    if (p.chunked == 1u) p.s_shift = 5;
+    while (p.chunked == 2u && (1u << p.s_shift) < s) ++p.s_shift;
     p.explicit_q0 = packets && primary_packet_hitlist(p) ? 1u : 0u;
     uint32_t* fb = p.st.counters + 4 * (size_t)(max_b + 1);  // {fall-back count, fall-back work counter}
     if (packets) {

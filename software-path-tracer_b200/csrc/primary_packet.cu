@@ -94,8 +94,14 @@ constexpr uint32_t kWarpSmem = kNodeBytes + kTriSlots * 48u;
 // warps, profiles/r01_notes.md).  To keep the queue in image order without a global atomic per packet, a CTA claims
 // TILES of 64 consecutive packets (one 8x8 pixel tile of one chunk group) and appends descriptors to the tile's own
 // region through a shared-memory counter; hitlist_scan / hitlist_expand then lay the regions out in tile order.
-template <bool kCount, int kRays, bool kList>
+//
+// kMini (kRays == 1; passes of 1, 2, 4, 8 or 16 samples, slot-major path ids, kernels.h): a packet is 32 CONSECUTIVE IDS =
+// 32 / S neighbouring pixels x S samples, so every lane has its own pixel; the bounding planes come from the rays' own
+// directions as before, they are just wider.  Lanes on padding slots (outside the image) duplicate a valid lane's ray
+// and store no result.  Precondition: every slot is owned (no partition, or the compacted one).
+template <bool kCount, int kRays, bool kList, bool kMini>
 __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6 : 4)) primary_packet_kernel(const PacketArgs a) {
+  static_assert(!kMini || kRays == 1, "multi-pixel packets carry one ray per lane");
   __shared__ uint32_t s_blk, s_cnt;
   __shared__ __align__(16) unsigned char s_warp[kPacketWarps * kWarpSmem];
   __shared__ uint8_t s_lut[8 * 256];
@@ -104,7 +110,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   const PassParams& p = a.p;
   const unsigned lane = threadIdx.x & 31u;
   const uint32_t n_warps = gridDim.x * kPacketWarps;
-  const uint32_t n_tasks = p.n_slots * (p.samples / (32u * kRays));
+  const uint32_t n_tasks = kMini ? (p.n_slots << p.s_shift) >> 5 : p.n_slots * (p.samples / (32u * kRays));
   const int ax_k = a.axis_k, ax_a = (ax_k + 1) % 3, ax_b = (ax_k + 2) % 3;
   const float sigma = a.sigma;
   const f3 O = p.cam.origin;
@@ -136,12 +142,25 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
   uint32_t done_rays = 0, n_nodes = 0, n_tris = 0, n_bail = 0, sky_rays = 0;
 
   auto process = [&](const uint32_t task) {
-    const uint32_t chunk = fd_div(p.fd_slots, task), slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
-    uint32_t x, y;
-    if (!slot_pixel(p, slot, x, y) || (!p.dense && !owns_pixel(p.im, x, y))) return;  // warp-uniform
+    uint32_t chunk = 0, slot, x, y, id0, s_mini = 0;
+    bool valid = true;  // kMini: this lane's slot is a pixel of the image
+    if constexpr (kMini) {
+      id0 = task * 32u + lane;  // slot-major path id (kernels.h slot_sample_id())
+      slot = id0 >> p.s_shift;
+      s_mini = id0 & ((1u << p.s_shift) - 1u);
+      valid = slot_pixel(p, slot, x, y);
+      const unsigned vm = __ballot_sync(kFull, valid);
+      if (vm == 0u) return;
+      const int src = __ffs(vm) - 1;  // padding lanes trace a copy of a valid lane's ray
+      const uint32_t sx = __shfl_sync(kFull, x, src), sy = __shfl_sync(kFull, y, src), ss = __shfl_sync(kFull, s_mini, src);
+      if (!valid) x = sx, y = sy, s_mini = ss;
+    } else {
+      chunk = fd_div(p.fd_slots, task), slot = task - chunk * p.n_slots;  // slots go tile by tile (kernels.h)
+      if (!slot_pixel(p, slot, x, y) || (!p.dense && !owns_pixel(p.im, x, y))) return;  // warp-uniform
+      id0 = ((chunk * kRays) * p.n_slots + slot) * 32u + lane;  // chunked path id (kernels.h path_id())
+    }
     const uint32_t pixel = y * p.im.width + x;
     // ---- the 32 * kRays rays (K1); ray j of a lane is sample 32 * (chunk * kRays + j) + lane ----
-    const uint32_t id0 = ((chunk * kRays) * p.n_slots + slot) * 32u + lane;  // chunked path id (kernels.h path_id())
     const uint32_t id_step = p.n_slots * 32u;                                // to the same lane of the next chunk
     f3 dir[kRays];
     float w[kRays];  // depth per unit t
@@ -149,7 +168,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
     bool bail = false;
 #pragma unroll
     for (int j = 0; j < kRays; ++j) {
-      const uint32_t s = (chunk * kRays + (uint32_t)j) * 32u + lane;
+      const uint32_t s = kMini ? s_mini : (chunk * kRays + (uint32_t)j) * 32u + lane;
       const uint32_t id = id0 + (uint32_t)j * id_step;
       const uint32_t frame = p.first_frame + s * p.frame_stride;
       float jx = 0.0f, jy = 0.0f;
@@ -160,7 +179,7 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       dir[j] = primary_dir(p.cam, p.im, x, y, jx, jy);
       // the origin {camera, tnear} of a camera ray is implied and queue 0 is the identity when every pixel is owned
       // (shade_kernel, wavefront.cu): neither is stored; the direction is stored at the end, if anything still needs it
-      if (!kList && !all_slots_owned(p)) {
+      if (!kMini && !kList && !all_slots_owned(p)) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(p.st.counters + slot_queue_count(0), 32u);
         base = __shfl_sync(kFull, base, 0);
@@ -298,14 +317,17 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
 #pragma unroll
       for (int j = 0; j < kRays; ++j) {
         const f3 L = mk3(0.f, 0.f, 0.f) + mk3(1.0f, 1.0f, 1.0f) * (sky_radiance(p.ip, dir[j]) * p.ip.sky_scale);
-        p.st.L[id0 + (uint32_t)j * id_step] = make_float4(L.x, L.y, L.z, 0.f);
+        if (!kMini || valid) p.st.L[id0 + (uint32_t)j * id_step] = make_float4(L.x, L.y, L.z, 0.f);
       }
-      if (p.aov_prim != nullptr && chunk == 0u && lane == 0u) {  // sample 0 of the pixel is ray 0 of lane 0
+      // sample 0 of the pixel: ray 0 of lane 0 of chunk 0, or (kMini) the lane whose sample index is 0
+      if (p.aov_prim != nullptr && (kMini ? (valid && s_mini == 0u) : (chunk == 0u && lane == 0u))) {
         p.aov_prim[pixel] = 0xFFFFFFFFu;
         p.aov_t[pixel] = __int_as_float(0x7f800000);
       }
-      sky_rays += (uint32_t)kRays;
-      done_rays += (uint32_t)kRays;
+      if (!kMini || valid) {
+        sky_rays += (uint32_t)kRays;
+        done_rays += (uint32_t)kRays;
+      }
       return;
     }
 #pragma unroll
@@ -315,30 +337,42 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       uint32_t pos = 0;
       if (lane == 0) pos = atomicAdd(&s_cnt, (uint32_t)kRays);
       pos = __shfl_sync(kFull, pos, 0);
-      if (lane < (uint32_t)kRays) a.desc[(size_t)s_blk * (64u * kRays) + pos + lane] = (id0 + lane * id_step) >> 5;
+      if (lane < (uint32_t)kRays) a.desc[(size_t)s_blk * (64u * kRays) + pos + lane] = kMini ? task : (id0 + lane * id_step) >> 5;
     }
     if (!bail) {
 #pragma unroll
       for (int j = 0; j < kRays; ++j)
         p.st.hit[id0 + (uint32_t)j * id_step] =
             make_uint2(__float_as_uint(hit[j].tri == 0xFFFFFFFFu ? __int_as_float(0x7f800000) : hit[j].t), hit[j].tri);
-      done_rays += (uint32_t)kRays;
+      if (!kMini || valid) done_rays += (uint32_t)kRays;
     } else {
-      uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(a.fb_count, 32u * kRays);
-      base = __shfl_sync(kFull, base, 0);
+      if constexpr (kMini) {  // only the lanes that are pixels go to the per-ray kernel, so that its ray count stays exact
+        const unsigned vm = __ballot_sync(kFull, valid);
+        const uint32_t rank = (uint32_t)__popc(vm & ((1u << lane) - 1u));
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(a.fb_count, (uint32_t)__popc(vm));
+        base = __shfl_sync(kFull, base, 0);
+        if (valid) {
+          a.fb_queue[base + rank] = id0;
+          p.st.ray_o[id0] = make_float4(O.x, O.y, O.z, p.ip.tnear);
+        }
+      } else {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(a.fb_count, 32u * kRays);
+        base = __shfl_sync(kFull, base, 0);
 #pragma unroll
-      for (int j = 0; j < kRays; ++j) {
-        const uint32_t id = id0 + (uint32_t)j * id_step;
-        a.fb_queue[base + 32u * (uint32_t)j + lane] = id;
-        p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);  // the per-ray kernel reads its rays from memory
+        for (int j = 0; j < kRays; ++j) {
+          const uint32_t id = id0 + (uint32_t)j * id_step;
+          a.fb_queue[base + 32u * (uint32_t)j + lane] = id;
+          p.st.ray_o[id] = make_float4(O.x, O.y, O.z, p.ip.tnear);  // the per-ray kernel reads its rays from memory
+        }
       }
       if (kCount) ++n_bail;
     }
   };
 
   if constexpr (kList) {
-    const uint32_t n_blocks = n_tasks >> 6;  // n_slots is a multiple of 64
+    const uint32_t n_blocks = kMini ? (n_tasks + 63u) >> 6 : n_tasks >> 6;  // n_slots is a multiple of 64: whole tiles unless kMini
     for (;;) {
       __syncthreads();  // the previous tile's count has been written
       if (threadIdx.x == 0) {
@@ -348,14 +382,15 @@ __global__ void __launch_bounds__(kPacketBlock, kRays == 1 ? 8 : (kRays == 2 ? 6
       __syncthreads();
       const uint32_t blk = s_blk;
       if (blk >= n_blocks) break;
-      for (uint32_t t = threadIdx.x >> 5; t < 64u; t += kPacketWarps) process((blk << 6) + t);
+      for (uint32_t t = threadIdx.x >> 5; t < 64u; t += kPacketWarps)
+        if (!kMini || (blk << 6) + t < n_tasks) process((blk << 6) + t);
       __syncthreads();
       if (threadIdx.x == 0) a.block_hits[blk] = s_cnt;
     }
   } else {
     for (uint32_t task = blockIdx.x * kPacketWarps + (threadIdx.x >> 5); task < n_tasks; task += n_warps) process(task);
   }
-  if (!kList && all_slots_owned(p) && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;
+  if (!kList && all_slots_owned(p) && blockIdx.x == 0 && threadIdx.x == 0) p.st.counters[slot_queue_count(0)] = p.n_slots * p.samples;  // (also the padding ids: the shade kernel skips them)
   const uint64_t wr = warp_sum_u32(done_rays);
   if (lane == 0 && wr) {
     atomicAdd(&p.counters[kCntRays], (unsigned long long)wr);
@@ -410,20 +445,38 @@ __global__ void __launch_bounds__(128) hitlist_expand_kernel(const uint32_t* __r
 
 }  // namespace
 
+bool primary_packet_shape(uint32_t samples) {
+  return (samples >= 32u && samples % 32u == 0u) || samples == 1u || samples == 2u || samples == 4u || samples == 8u || samples == 16u;
+}
+
 // The bounce-0 hit list applies when every slot of the pass is owned: no partition, or the compacted slots of a tile
 // partition (kernels.h); a sparse partition keeps an explicit queue built with one atomic per packet.
 bool primary_packet_hitlist(const PassParams& p) {
   const char* e = getenv("CUDAPT_PACKET_HITLIST");  // read per pass: tests toggle it
-  return (e ? atoi(e) : 1) != 0 && all_slots_owned(p) && primary_packets_enabled(p);
+  if ((e ? atoi(e) : 1) == 0 || !all_slots_owned(p) || !primary_packets_enabled(p)) return false;
+  if (p.samples % 32u != 0u) {
+    // multi-pixel packets: descriptors (one per packet, in blocks of 64) + per-block counts and offsets must fit the shadow
+    // queue of the pass (one word per path) -- they do not for images of a tile or two
+    const uint64_t n_tasks = ((uint64_t)p.n_slots * p.samples) >> 5, n_blocks = (n_tasks + 63u) >> 6;
+    if (n_blocks * 64u + 2u * n_blocks > (uint64_t)p.n_slots * p.samples) return false;
+  }
+  return true;
 }
 
-// Packets apply to a pass whose sample count is a multiple of 32 (one warp = 32 samples of one pixel);
-// CUDAPT_PRIMARY_PACKETS=0 switches them off.
+// Packets apply to a pass of 32 k samples (one warp = 32 samples of one pixel, k = 1, 2 or 4 rays per lane) and to a pass
+// of 1, 2, 4, 8 or 16 samples (one warp = 32 / S neighbouring pixels x S samples) when every slot of the pass is owned;
+// CUDAPT_PRIMARY_PACKETS=0 switches them off; CUDAPT_PACKET_MINI: see below.
 bool primary_packets_enabled(const PassParams& p) {
   const char* e = getenv("CUDAPT_PRIMARY_PACKETS");  // read per pass: tests toggle it
   const int on = e ? atoi(e) : 1;
   // a thin lens gives every ray its own origin: no common apex, no packets
-  return on != 0 && p.samples >= 32u && p.samples % 32u == 0u && !(p.cam.lens_radius > 0.0f);
+  if (on == 0 || p.cam.lens_radius > 0.0f || !primary_packet_shape(p.samples)) return false;
+  if (p.samples % 32u == 0u) return true;
+  // measured on C3 at 1920x1080 (profiles/r02m_mini_probe_c3.log): 16 samples per pass -24 %, 8 -15 %, 4 neutral, 1 +54 %
+  // (an 8x4-pixel frustum tests 11 triangles per packet) -> on from 8 samples; CUDAPT_PACKET_MINI=1 forces 1..16, =0 off
+  const char* m = getenv("CUDAPT_PACKET_MINI");
+  const bool wanted = m ? atoi(m) != 0 : p.samples >= 8u;
+  return wanted && all_slots_owned(p);
 }
 
 cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint32_t* fb_count, bool counting, int sm_count,
@@ -442,33 +495,40 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
   a.sigma = f[k] < 0.0f ? -1.0f : 1.0f;
   a.budget = budget;
   const char* re = getenv("CUDAPT_PACKET_RAYS");  // rays per lane: 1, 2 or 4 (default: the largest that divides the pass)
+  const bool mini = p.chunked == 2u;
   const uint32_t chunks = p.samples / 32u;
   int rays = re ? atoi(re) : 4;
-  rays = rays >= 4 && chunks % 4u == 0u ? 4 : (rays >= 2 && chunks % 2u == 0u ? 2 : 1);
-  const uint32_t n_tasks = p.n_slots * (chunks / (uint32_t)rays);
+  rays = mini ? 1 : (rays >= 4 && chunks % 4u == 0u ? 4 : (rays >= 2 && chunks % 2u == 0u ? 2 : 1));
+  const uint32_t n_tasks = mini ? (uint32_t)(((uint64_t)p.n_slots * p.samples) >> 5) : p.n_slots * (chunks / (uint32_t)rays);
   const uint32_t warps_per_cta = kPacketWarps;
   uint32_t grid = (uint32_t)sm_count * (rays == 1 ? 8u : (rays == 2 ? 6u : 4u));
   const uint32_t need = (n_tasks + warps_per_cta - 1) / warps_per_cta;
   if (need < grid) grid = need ? need : 1u;
   // hit list: descriptors, per-tile counts and offsets live in the (still unused) shadow queue of the pass
   const bool list = p.explicit_q0 != 0u;
-  const uint32_t n_blocks = n_tasks >> 6, n_desc = p.n_slots * chunks;
+  const uint32_t n_blocks = (n_tasks + 63u) >> 6, n_desc = mini ? n_blocks * 64u : p.n_slots * chunks;
   a.block_counter = fb_count + 2;  // free word of the fall-back counter block, zeroed with the pass's counters
   a.desc = p.st.shadow_queue;
   a.block_hits = p.st.shadow_queue + n_desc;
   uint32_t* offsets = a.block_hits + n_blocks;
-#define PK_LAUNCH2(R, L)                                                    \
-  if (counting)                                                             \
-    primary_packet_kernel<true, R, L><<<grid, kPacketBlock, 0, s>>>(a);     \
-  else                                                                      \
-    primary_packet_kernel<false, R, L><<<grid, kPacketBlock, 0, s>>>(a)
-#define PK_LAUNCH(R)          \
-  if (list) {                 \
-    PK_LAUNCH2(R, true);      \
-  } else {                    \
-    PK_LAUNCH2(R, false);     \
+#define PK_LAUNCH3(R, L, M)                                                    \
+  if (counting)                                                                \
+    primary_packet_kernel<true, R, L, M><<<grid, kPacketBlock, 0, s>>>(a);     \
+  else                                                                         \
+    primary_packet_kernel<false, R, L, M><<<grid, kPacketBlock, 0, s>>>(a)
+#define PK_LAUNCH(R)             \
+  if (list) {                    \
+    PK_LAUNCH3(R, true, false);  \
+  } else {                       \
+    PK_LAUNCH3(R, false, false); \
   }
-  if (rays == 4) {
+  if (mini) {
+    if (list) {
+      PK_LAUNCH3(1, true, true);
+    } else {
+      PK_LAUNCH3(1, false, true);
+    }
+  } else if (rays == 4) {
     PK_LAUNCH(4);
   } else if (rays == 2) {
     PK_LAUNCH(2);
@@ -476,7 +536,7 @@ cudaError_t launch_primary_packets(const PassParams& p, uint32_t* fb_queue, uint
     PK_LAUNCH(1);
   }
 #undef PK_LAUNCH
-#undef PK_LAUNCH2
+#undef PK_LAUNCH3
   if (list) {
     hitlist_scan_kernel<<<1, 1024, 0, s>>>(a.block_hits, n_blocks, offsets, p.st.counters + slot_queue_count(0));
     hitlist_expand_kernel<<<(uint32_t)sm_count * 8u, 128, 0, s>>>(a.desc, a.block_hits, offsets, n_blocks, 64u * (uint32_t)rays, p.st.queue[0]);

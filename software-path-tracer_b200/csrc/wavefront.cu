@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(kShadeBlock) accumulate_kernel(const PassParam
       const uint32_t pixel = y * p.im.width + x;
       float4 acc = p.accum[pixel];
       for (uint32_t s = 0; s < p.samples; ++s) {
-        const float4 l = p.st.L[(((s >> 5) * p.n_slots + g) << 5) | (s & 31u)];
+        const float4 l = p.st.L[slot_sample_id(p, g, s)];
         acc.x += l.x;
         acc.y += l.y;
         acc.z += l.z;

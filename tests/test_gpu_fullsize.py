@@ -115,7 +115,7 @@ def test_c4_reduced_per_ray_pass(pt, oracle, small_rocks):
 # ---- configs[3] at its full size ---------------------------------------------------------------------------------
 def test_c4_full_size_tile_share(pt, oracle, scenes):
     """20 000 002 triangles (1.3 GB BVH, > L2), 1920x1080, depth 16: ONE 128-sample pass exactly as `bench.py --workload
-    c4` runs it (4 rays per lane, hit list, fall-back queue), and a 2-sample per-ray pass, each against a 1/256
+    c4` runs it (4 rays per lane, hit list, fall-back queue), and a 3-sample per-ray pass, each against a 1/256
     interleaved-tile share rendered by the twin at the same sample counts."""
     scene = scenes.rock_field()
     assert len(scene[1]) == 20_000_002
@@ -125,9 +125,9 @@ def test_c4_full_size_tile_share(pt, oracle, scenes):
     assert st.packet_rays > 0.9 * W * H * 128 and st.paths == W * H * 128
     n = compare_share(oracle, twin, acc, prim, t, W, H, 128, 1.0, C4_CFG, (0, 256, 8, 8), "c4 1920x1080 128 spp (packets)")
     assert n >= 8000
-    acc, prim, t, st = gpu_render(pt, scene, W, H, 2, 2, 1.0, C4_CFG)
+    acc, prim, t, st = gpu_render(pt, scene, W, H, 3, 3, 1.0, C4_CFG)   # 3 samples: no packet shape -> raygen + per-ray kernel
     assert st.packet_rays == 0
-    compare_share(oracle, twin, acc, prim, t, W, H, 2, 1.0, C4_CFG, (101, 256, 8, 8), "c4 1920x1080 2 spp (per-ray)")
+    compare_share(oracle, twin, acc, prim, t, W, H, 3, 1.0, C4_CFG, (101, 256, 8, 8), "c4 1920x1080 3 spp (per-ray)")
     twin.close()
 
 
@@ -137,7 +137,7 @@ C3_CFG = dict(rng_mode=1, max_bounces=8, jitter=1, seed=3)
 
 def test_c3_full_size_tile_share(pt, oracle, scenes):
     """1 002 528 triangles, 1920x1080: the 64-sample step of the default bench (2 rays per lane, hit list) and a
-    2-sample per-ray pass, against 1/64 and 1/256 tile shares of the twin."""
+    3-sample per-ray pass and a 16-sample pass of multi-pixel packets, against 1/64 and 1/256 tile shares of the twin."""
     scene = scenes.heightfield()
     assert len(scene[1]) == 1_002_528
     twin = oracle.TwinMesh(*scene)
@@ -146,9 +146,12 @@ def test_c3_full_size_tile_share(pt, oracle, scenes):
     assert st.packet_rays > 0.99 * W * H * 64
     n = compare_share(oracle, twin, acc, prim, t, W, H, 64, 1.0, C3_CFG, (5, 64, 8, 8), "c3 1920x1080 64 spp (packets)")
     assert n >= 32000
-    acc, prim, t, st = gpu_render(pt, scene, W, H, 2, 2, 1.0, C3_CFG)
+    acc, prim, t, st = gpu_render(pt, scene, W, H, 3, 3, 1.0, C3_CFG)   # 3 samples: no packet shape -> raygen + per-ray kernel
     assert st.packet_rays == 0
-    compare_share(oracle, twin, acc, prim, t, W, H, 2, 1.0, C3_CFG, (17, 256, 8, 8), "c3 1920x1080 2 spp (per-ray)")
+    compare_share(oracle, twin, acc, prim, t, W, H, 3, 1.0, C3_CFG, (17, 256, 8, 8), "c3 1920x1080 3 spp (per-ray)")
+    acc, prim, t, st = gpu_render(pt, scene, W, H, 16, 16, 1.0, C3_CFG)  # 16 samples: packets of 2 pixels x 16 samples
+    assert st.packet_rays > 0.9 * W * H * 16
+    compare_share(oracle, twin, acc, prim, t, W, H, 16, 1.0, C3_CFG, (33, 256, 8, 8), "c3 1920x1080 16 spp (multi-pixel packets)")
     twin.close()
 
 

@@ -233,3 +233,61 @@ def test_pass_of_512_samples_under_a_tile_partition(pt, scenes):
     assert np.array_equal(bits(total), bits(full)) and paths == fst.paths == W * H * N
     with pytest.raises(pt.CudaptError):
         pt.PathTracer(pt.default_config(rng_mode=1, samples_per_pass=1025))
+
+
+@pytest.mark.parametrize("S", [1, 2, 4, 8, 16])
+def test_multi_pixel_packets_equal_per_ray_path(pt, oracle, scenes, S, monkeypatch):
+    """Passes of 1, 2, 4, 8 or 16 samples trace their camera rays as packets of 32 / S neighbouring pixels x S samples
+    (primary_packet.cu kMini, slot-major path ids) -- what a viewer that renders one sample per call gets.  Accumulation,
+    primary-hit AOVs and counters must equal the raygen + per-ray path (CUDAPT_PACKET_MINI=0) bit for bit, with the hit
+    list on and off, with a budget that sends every packet to the per-ray kernel, on an image whose size is not a
+    multiple of the 8x8 slot tiles, and the twin's image."""
+    scene = scenes.heightfield(n_quads=64)
+    W, H, N = 203, 117, 3 * S          # three passes
+    kw = dict(max_bounces=4, jitter=1, seed=23)
+    monkeypatch.setenv("CUDAPT_PACKET_MINI", "0")
+    a0, p0, t0, s0 = render(pt, scene, W, H, N, S, **kw)
+    assert s0.packet_rays == 0
+    monkeypatch.setenv("CUDAPT_PACKET_MINI", "1")
+    for hitlist, budget in (("1", "400"), ("0", "400"), ("1", "0")):
+        monkeypatch.setenv("CUDAPT_PACKET_HITLIST", hitlist)
+        monkeypatch.setenv("CUDAPT_PACKET_BUDGET", budget)
+        a1, p1, t1, s1 = render(pt, scene, W, H, N, S, **kw)
+        assert np.array_equal(bits(a1), bits(a0)) and np.array_equal(p1, p0) and np.array_equal(bits(t1), bits(t0)), (hitlist, budget)
+        assert (s1.paths, s1.rays, s1.shade_invocations) == (s0.paths, s0.rays, s0.shade_invocations)
+        if budget != "0":
+            assert s1.packet_rays > 0.9 * W * H * N
+    monkeypatch.delenv("CUDAPT_PACKET_HITLIST")
+    monkeypatch.delenv("CUDAPT_PACKET_BUDGET")
+    want, widx, wt, _ = oracle.TwinMesh(*scene).render(oracle.twin_params(W, H, rng_mode=1, **kw), N, want_primary=True)
+    got = np.where(p0 == 0xFFFFFFFF, -1, p0.astype(np.int64))
+    assert np.array_equal(got, widx) and np.array_equal(bits(t0), bits(wt)) and np.array_equal(bits(a0), bits(want))
+
+
+def test_multi_pixel_packets_tiny_images_partition_and_cornell(pt, scenes, monkeypatch):
+    """Images of one tile or less (the hit list's scratch does not fit: identity queue), a compacted 3-rank partition with
+    4-sample passes, and the closed Cornell box with NEE at 1 sample per pass."""
+    hf = scenes.heightfield(n_quads=32)
+    for W, H in ((1, 1), (7, 3), (8, 8), (33, 17)):
+        out = {}
+        for on in ("0", "1"):
+            monkeypatch.setenv("CUDAPT_PACKET_MINI", on)
+            out[on] = render(pt, hf, W, H, 4, 2, max_bounces=3, jitter=1, seed=5)
+        assert np.array_equal(bits(out["0"][0]), bits(out["1"][0])) and np.array_equal(out["0"][1], out["1"][1]), (W, H)
+    monkeypatch.setenv("CUDAPT_PACKET_MINI", "1")
+    kw = dict(max_bounces=4, jitter=1, seed=7)
+    full, fprim, ft, fst = render(pt, hf, 203, 117, 8, 4, **kw)
+    total = np.zeros_like(full)
+    packet_rays = 0
+    for r in range(3):
+        a, _, _, st = render(pt, hf, 203, 117, 8, 4, part=(r, 3, 16, 8), **kw)
+        total += a
+        packet_rays += st.packet_rays
+    assert np.array_equal(bits(total), bits(full)) and packet_rays > 0.9 * 203 * 117 * 8
+    box = scenes.cornell_box(sphere_res=8)
+    ckw = dict(max_bounces=5, jitter=1, nee=1, sky_scale=0.0, seed=5)
+    out = {}
+    for on in ("0", "1"):
+        monkeypatch.setenv("CUDAPT_PACKET_MINI", on)
+        out[on] = render(pt, box, 96, 54, 6, 1, cam=dict(tan_half_fov=0.36), **ckw)
+    assert np.array_equal(bits(out["0"][0]), bits(out["1"][0])) and out["1"][3].packet_rays > 0 and out["0"][3].packet_rays == 0
