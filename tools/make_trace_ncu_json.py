@@ -27,7 +27,8 @@ M = {"dur_us": "gpu__time_duration.sum", "inst": "smsp__inst_executed.sum",
      "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
      "l1_hit_pct": "l1tex__t_sector_hit_rate.pct", "l2_hit_pct": "lts__t_sector_hit_rate.pct",
      "dram_read": "dram__bytes_read.sum", "dram_write": "dram__bytes_write.sum",
-     "dram_pct_of_peak": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"}
+     "dram_pct_of_peak": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+     "l2_sectors": "lts__t_sectors.sum", "l1_sectors": "l1tex__t_sectors.sum", "l1_miss_sectors": "l1tex__t_sectors_lookup_miss.sum"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "us": 1.0, "ms": 1e3, "ns": 1e-3, "s": 1e6,
         "usecond": 1.0, "msecond": 1e3, "nsecond": 1e-3, "second": 1e6}
 
@@ -40,8 +41,8 @@ def rows_of(rep):
     for r in rows[2:]:
         d = {"kernel": r[hdr.index("Kernel Name")]}
         for k, name in M.items():
-            if name in hdr:
-                i = hdr.index(name)
+            i = next((j for j, h in enumerate(hdr) if h == name or h.endswith("." + name)), None)  # some carry a section prefix
+            if i is not None and r[i] != "":
                 d[k] = float(r[i].replace(",", "")) * UNIT.get(units[i], 1.0)
         res.append(d)
     return res
@@ -94,7 +95,23 @@ def main():
                      "longest_launch_us": top["dur_us"], "warp_instructions_longest_launch": top["inst"],
                      **{k: top[k] for k in ("issue_slot_utilisation_pct", "lanes_per_instruction", "alu_pipe_pct", "fma_pipe_pct",
                                             "warps_active_pct", "l1_hit_pct", "l2_hit_pct", "dram_pct_of_peak") if k in top}}
+        # achieved bandwidth at each level during the longest launch (32-byte sectors): what the loads ask of L1, what L1
+        # passes on to L2 (its misses; reads), all L2 traffic (incl. stores and the other die's fabric), and DRAM
+        sec = top["dur_us"] * 1e-6
+        if "l1_sectors" in top:
+            out[name]["l1_request_GBps"] = top["l1_sectors"] * 32.0 / sec / 1e9
+        if "l1_miss_sectors" in top:
+            out[name]["l1_to_l2_GBps"] = top["l1_miss_sectors"] * 32.0 / sec / 1e9
+        if "l2_sectors" in top:
+            out[name]["l2_GBps"] = top["l2_sectors"] * 32.0 / sec / 1e9
+        out[name]["dram_GBps"] = (top["dram_read"] + top["dram_write"]) / sec / 1e9
     path = os.path.join(ROOT, "profiles", "trace_kernel_ncu.json")
+    if os.path.exists(path):  # keep the workloads of an earlier capture of the SAME build
+        old = json.load(open(path))
+        if old.get("build_hash") == out["build_hash"]:
+            for k, v in old.items():
+                if isinstance(v, dict) and k not in out:
+                    out[k] = v
     json.dump(out, open(path, "w"), indent=1)
     print(json.dumps(out, indent=1))
 
